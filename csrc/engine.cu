@@ -1,0 +1,187 @@
+// engine.cu — model lifetime and the generate entry point.
+//
+//   b200gru_model_create   <- namegen_initialize (ref:359-618)
+//   b200gru_generate       <- namegen, one rank's slice (ref:627-890)
+//   b200gru_model_destroy  <- namegen_finalize (ref:897-1033)
+//
+// Differences from the reference that are deliberate: the device is chosen
+// explicitly (the reference never calls cudaSetDevice); every buffer is
+// allocated once here, checked, tracked and freed (the reference leaks the
+// file buffer, double-allocates gb_fc ref:571-577, and cudaFree()s a host
+// pointer ref:1017); nothing is allocated in generate.
+#include "model.hpp"
+#include "sm100_ptx.cuh"
+
+using namespace b200gru;
+
+namespace {
+
+template <typename T>
+int dev_alloc(b200gru_model *m, T **out, size_t count) {
+  void *p = nullptr;
+  size_t bytes = count * sizeof(T);
+  if (bytes == 0) bytes = sizeof(T);
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess)
+    return fail(B200GRU_ERR_CUDA, "cudaMalloc(%zu bytes) failed: %s", bytes,
+                cudaGetErrorString(e));
+  m->allocs.push_back(p);
+  m->device_bytes += (int64_t)bytes;
+  *out = static_cast<T *>(p);
+  return 0;
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+__global__ void wait_flags_kernel(const uint32_t *flags, int n, uint32_t value) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    while (sm100::ld_acquire_sys(flags + i) != value) __nanosleep(200);
+  }
+  __syncthreads();
+  __threadfence_system();
+}
+
+int create_impl(b200gru_model *m, const float *params_host) {
+  const b200gru_config &c = m->cfg;
+  const int H = c.hidden, C = c.num_char, L = c.num_layers, E = c.emb_dim;
+  LayoutIndex ix(L);
+  const int64_t n_params = m->lay.back().offset + m->lay.back().size;
+
+  // C8: upload.  One copy of the whole file instead of 28 cudaMemcpy calls.
+  if (int rc = dev_alloc(m, &m->params, (size_t)n_params)) return rc;
+  B200_CUDA(cudaMemcpy(m->params, params_host, sizeof(float) * n_params,
+                       cudaMemcpyHostToDevice));
+  m->b_fc = m->P(ix.b_fc());
+
+  // C9: activation buffers, sized once.
+  m->chunk = m->max_batch < kExactChunk ? m->max_batch : kExactChunk;
+  if (int rc = dev_alloc(m, &m->t0_raw, (size_t)C * 3 * H)) return rc;
+  if (int rc = dev_alloc(m, &m->g_ih, (size_t)m->chunk * 3 * H)) return rc;
+  if (int rc = dev_alloc(m, &m->g_hh, (size_t)m->chunk * 3 * H)) return rc;
+  if (int rc = dev_alloc(m, &m->h32, (size_t)L * m->chunk * H)) return rc;
+  if (int rc = dev_alloc(m, &m->logits, (size_t)m->bpad * C)) return rc;
+  if (int rc = dev_alloc(m, &m->chars, (size_t)m->bpad)) return rc;
+  if (int rc = dev_alloc(m, &m->alive, (size_t)m->bpad)) return rc;
+  B200_CUDA(cudaMemset(m->logits, 0, sizeof(float) * (size_t)m->bpad * C));
+
+  // Layer-0 input projection as a table: the embedding (ref:112-118) followed
+  // by the three W_i*0 matvecs (ref:676,:702,:729) only depends on the
+  // character id, so it is computed once per id.  Same left-to-right fma
+  // order => same bits as doing it per step.
+  if (int rc = exact_sgemm_tn(m->P(ix.emb()), m->P(ix.w_i(0, 0)), m->t0_raw, C,
+                              3 * H, E, 0))
+    return rc;
+
+  // Tensor-core path needs 64-aligned hidden size and a single-UMMA FC.
+  m->tc_ok = (H % kUnitBlock == 0) && (C % 16 == 0) && C >= 16 && C <= 256;
+  if (m->tc_ok)
+    if (int rc = tc_prepare(m)) return rc;
+  B200_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200gru_model_create(const b200gru_config *cfg, const float *params,
+                         int device, int max_batch, b200gru_model **out) {
+  if (int rc = validate_config(cfg)) return rc;
+  B200_REQUIRE(params && out, "null argument");
+  B200_REQUIRE(max_batch > 0, "max_batch must be positive");
+  int ndev = 0;
+  B200_CUDA(cudaGetDeviceCount(&ndev));
+  B200_REQUIRE(device >= 0 && device < ndev, "device %d of %d", device, ndev);
+  DeviceGuard guard(device);
+  auto *m = new b200gru_model();
+  m->cfg = *cfg;
+  m->device = device;
+  m->max_batch = max_batch;
+  m->bpad = (max_batch + kTileM - 1) / kTileM * kTileM;
+  m->lay = build_layout(*cfg);
+  int rc = create_impl(m, params);
+  if (rc) {
+    for (void *p : m->allocs) cudaFree(p);
+    delete m;
+    return rc;
+  }
+  *out = m;
+  return 0;
+}
+
+int b200gru_model_destroy(b200gru_model *m) {
+  if (!m) return 0;
+  DeviceGuard guard(m->device);
+  cudaError_t first = cudaDeviceSynchronize();
+  for (void *p : m->allocs) {
+    cudaError_t e = cudaFree(p);
+    if (first == cudaSuccess) first = e;
+  }
+  delete m;
+  if (first != cudaSuccess)
+    return fail(B200GRU_ERR_CUDA, "destroy: %s", cudaGetErrorString(first));
+  return 0;
+}
+
+int64_t b200gru_model_device_bytes(const b200gru_model *m) {
+  return m ? m->device_bytes : 0;
+}
+
+int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
+                     void *stream) {
+  B200_REQUIRE(m && io, "null argument");
+  B200_REQUIRE(n >= 0 && n <= m->max_batch, "n=%d exceeds max_batch=%d", n,
+               m->max_batch);
+  B200_REQUIRE(io->rfloats && io->output, "io pointers are null");
+  DeviceGuard guard(m->device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  m->last_launches = 0;
+  if (n == 0 && !io->done_flag) return 0;
+  if (mode == B200GRU_MODE_EXACT) return exact_generate(m, n, io, s);
+  if (mode == B200GRU_MODE_TC) {
+    if (!m->tc_ok)
+      return fail(B200GRU_ERR_ARG,
+                  "tensor-core mode needs hidden %% 64 == 0 and num_char a "
+                  "multiple of 16 in [16,256] (got H=%d, C=%d)",
+                  m->cfg.hidden, m->cfg.num_char);
+    return tc_generate(m, n, io, s);
+  }
+  return fail(B200GRU_ERR_ARG, "unknown mode %d", mode);
+}
+
+int b200gru_last_launch_count(const b200gru_model *m) {
+  return m ? m->last_launches : 0;
+}
+
+int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
+                         void *stream) {
+  B200_REQUIRE(m && dst_device && n >= 0 && n <= m->bpad, "bad arguments");
+  DeviceGuard guard(m->device);
+  B200_CUDA(cudaMemcpyAsync(dst_device, m->logits,
+                            sizeof(float) * (size_t)n * m->cfg.num_char,
+                            cudaMemcpyDeviceToDevice,
+                            static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+int b200gru_wait_flags(const uint32_t *flags, int n, uint32_t value,
+                       void *stream) {
+  B200_REQUIRE(flags && n > 0, "bad arguments");
+  wait_flags_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flags, n,
+                                                                    value);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,77 @@
+// model.hpp — device-side model state (the reference's C5/C8/C9: raw float*
+// globals at ref:348-357 filled by ref:471-612).  Here it is one heap object
+// per model so several models / devices can coexist, every buffer is allocated
+// once in b200gru_model_create (the reference re-mallocs per call, ref:632),
+// and everything is released in b200gru_model_destroy.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <vector>
+
+#include "errors.hpp"
+#include "layout.hpp"
+
+namespace b200gru {
+
+constexpr int kTileM = 128;     // names per tensor-core tile
+constexpr int kUnitBlock = 64;  // hidden units per tile (x3 / x4 gate columns)
+constexpr int kExactChunk = 8192;
+
+struct TcLayer {
+  __nv_bfloat16 *w_ih = nullptr;  // packed [H/64][192][K]  (layers >= 1)
+  __nv_bfloat16 *w_hh = nullptr;  // packed [H/64][192][H]
+  float *bias = nullptr;          // [H/64][4][64]: b_r(+hr), b_z(+hz), b_in, b_hn
+  CUtensorMap map_w_ih, map_w_hh;
+  CUtensorMap map_h[2];           // A-operand maps over the two h buffers
+  __nv_bfloat16 *h[2] = {nullptr, nullptr};  // [bpad, H] ping-pong
+};
+
+}  // namespace b200gru
+
+struct b200gru_model {
+  b200gru_config cfg{};
+  int device = 0;
+  int max_batch = 0;
+  int bpad = 0;  // max_batch rounded up to kTileM
+  bool tc_ok = false;
+  std::vector<b200gru::TensorSpec> lay;
+  std::vector<void *> allocs;
+  int64_t device_bytes = 0;
+  int last_launches = 0;
+
+  float *params = nullptr;  // whole weight file, fp32
+  // --- exact (fp32 SIMT) path
+  int chunk = 0;
+  float *t0_raw = nullptr;  // [C, 3H]   W_ih0 . emb[c]   (no bias)
+  float *g_ih = nullptr;    // [chunk, 3H]
+  float *g_hh = nullptr;    // [chunk, 3H]
+  float *h32 = nullptr;     // [L, chunk, H]
+  // --- shared
+  float *logits = nullptr;  // [bpad, C]
+  int32_t *chars = nullptr; // [bpad]
+  uint8_t *alive = nullptr; // [bpad]
+  // --- tensor-core path
+  float *t0_tc = nullptr;   // [C, H/64, 3, 64], b_ih (+ b_hr, b_hz) folded
+  b200gru::TcLayer tc[B200GRU_MAX_LAYERS];
+  __nv_bfloat16 *w_fc = nullptr;  // [C, H] bf16
+  CUtensorMap map_w_fc;
+  const float *b_fc = nullptr;    // into params
+
+  const float *P(int k) const { return params + lay[k].offset; }
+};
+
+namespace b200gru {
+// exact path (gru_exact.cu)
+int exact_sgemm_tn(const float *a, const float *w, float *c, int m, int n,
+                   int k, cudaStream_t s);
+int exact_generate(b200gru_model *m, int n, const b200gru_io *io,
+                   cudaStream_t s);
+// tensor-core path (gru_tc_sm100.cu)
+int tc_prepare(b200gru_model *m);
+int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s);
+// TMA descriptor helper (tma_host.cu)
+int make_tmap_bf16_2d(CUtensorMap *map, const void *base, uint64_t rows,
+                      uint64_t cols, uint32_t box_rows, uint32_t box_cols);
+}  // namespace b200gru

@@ -1,0 +1,150 @@
+"""NameGenerator — the public model API.
+
+Mirrors the reference's three entry points (`/root/reference/namegensf.cu`):
+
+    namegen_initialize(N, rng_seed, parameter_fname)   :359  -> NameGenerator(...)
+    namegen(N, random_floats, output)                  :627  -> .generate(N, random_floats)
+    namegen_finalize()                                 :897  -> .finalize()
+
+`generate` keeps the reference's contract: `random_floats` is `N*MAX_LEN` host
+floats significant on the root rank, the result is `N x (MAX_LEN+1)` bytes on
+the root rank, names are split over ranks in contiguous blocks of `N // size`
+and the `N % size` tail stays zero (`:628-630`, `:640`).
+"""
+from __future__ import annotations
+
+import ctypes
+from pathlib import Path
+
+import torch
+
+from .. import _native
+from ..config import GRUConfig
+from ..parallel.partition import partition
+from ..utils import weights as W
+
+MODE_EXACT = 0
+MODE_TC = 1
+_MODES = {"exact": MODE_EXACT, "fp32": MODE_EXACT, "tc": MODE_TC, "bf16": MODE_TC}
+
+
+class NameGenerator:
+    """One rank's model instance on one GPU.
+
+    Parameters
+    ----------
+    cfg : GRUConfig
+    params : flat fp32 tensor in file order, or a path to the weight file
+    device : CUDA device index (default: current device).  The reference never
+        binds a device (`cudaSetDevice` is absent); here it is explicit.
+    max_batch : most names this rank will run in one `generate` call
+    mode : "tc"/"bf16" (tcgen05 tensor cores) or "exact"/"fp32" (bit-identical
+        to the CPU oracle)
+    comm : optional `parallel.dp.DPContext` for multi-GPU runs
+    """
+
+    def __init__(self, cfg: GRUConfig, params, device: int | None = None, max_batch: int = 4096,
+                 mode: str = "tc", comm=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("NameGenerator needs a CUDA device (use models.oracle / TorchNameGen on CPU)")
+        self.cfg = cfg
+        self.mode = _MODES[mode]
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.max_batch = int(max_batch)
+        self.comm = comm
+        if isinstance(params, (str, Path)):
+            params = W.load(params, cfg)
+        params = params.detach().to(torch.float32).contiguous().cpu()
+        if params.numel() != W.param_count(cfg):
+            raise ValueError(f"parameter vector has {params.numel()} floats, config needs {W.param_count(cfg)}")
+        self._lib = _native.lib()
+        handle = ctypes.c_void_p()
+        c = cfg.to_c()
+        _native.check(self._lib.b200gru_model_create(ctypes.byref(c), params.data_ptr(), self.device,
+                                                     self.max_batch, ctypes.byref(handle)), "model_create")
+        self._h = handle
+        dev = torch.device("cuda", self.device)
+        # device-side staging for the single-process path (root == this rank)
+        self._rf_dev = torch.empty(self.max_batch * cfg.max_len, dtype=torch.float32, device=dev)
+        self._out_dev = torch.zeros(self.max_batch, cfg.max_len + 1, dtype=torch.uint8, device=dev)
+        self._out_host = torch.zeros(self.max_batch, cfg.max_len + 1, dtype=torch.uint8).pin_memory()
+        self.last_launches = 0
+
+    # ------------------------------------------------------------------ core
+    def generate_device(self, rfloats_dev: torch.Tensor, n: int, out_dev: torch.Tensor | None = None,
+                        mode: str | None = None, done_flag_ptr: int = 0, done_value: int = 0) -> torch.Tensor:
+        """Generate `n` names from device-resident floats; asynchronous on the
+        current stream.  `rfloats_dev` / `out_dev` may live on a peer GPU."""
+        cfg = self.cfg
+        if n > self.max_batch:
+            raise ValueError(f"n={n} > max_batch={self.max_batch}")
+        if out_dev is None:
+            out_dev = self._out_dev
+        io = _native.CIo(rfloats_dev.data_ptr(), out_dev.data_ptr(), done_flag_ptr or None, done_value)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        m = self.mode if mode is None else _MODES[mode]
+        _native.check(self._lib.b200gru_generate(self._h, m, n, ctypes.byref(io), ctypes.c_void_p(stream)),
+                      "generate")
+        self.last_launches = self._lib.b200gru_last_launch_count(self._h)
+        return out_dev[:n]
+
+    def generate(self, n_names: int, random_floats: torch.Tensor, mode: str | None = None) -> torch.Tensor:
+        """namegen(): host floats in, host `uint8[n_names, max_len+1]` out."""
+        if self.comm is not None:
+            return self.comm.generate(self, n_names, random_floats, mode=mode)
+        cfg = self.cfg
+        need = n_names * cfg.max_len
+        rf = random_floats.reshape(-1)
+        if rf.numel() < need:
+            raise ValueError(f"random_floats has {rf.numel()} values, need {need}")
+        sl = partition(n_names, 1, 0)
+        with torch.cuda.device(self.device):
+            self._rf_dev[:need].copy_(rf[:need], non_blocking=True)
+            out = self.generate_device(self._rf_dev, sl.count, mode=mode)
+            host = self._out_host[:n_names]
+            host.copy_(out, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        return host.clone()
+
+    def debug_logits(self, n: int) -> torch.Tensor:
+        """Last step's pre-softmax FC outputs for the first `n` names."""
+        out = torch.empty(n, self.cfg.num_char, dtype=torch.float32, device=torch.device("cuda", self.device))
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _native.check(self._lib.b200gru_debug_logits(self._h, out.data_ptr(), n, ctypes.c_void_p(stream)))
+        return out
+
+    @property
+    def device_bytes(self) -> int:
+        return self._lib.b200gru_model_device_bytes(self._h)
+
+    def finalize(self) -> None:
+        if getattr(self, "_h", None):
+            _native.check(self._lib.b200gru_model_destroy(self._h), "model_destroy")
+            self._h = None
+
+    close = finalize
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.finalize()
+
+    def __del__(self):
+        try:
+            self.finalize()
+        except Exception:
+            pass
+
+
+def decode(rows: torch.Tensor, eos: int | None = None) -> list[bytes]:
+    """Rows of the output matrix as byte strings, cut at the first NUL (the way
+    a C caller would `printf("%s")` them) and optionally at EOS."""
+    out = []
+    for row in rows.cpu().numpy():
+        b = bytes(row.tolist())
+        b = b.split(b"\0", 1)[0]
+        if eos is not None and eos != 0:
+            b = b.split(bytes([eos]), 1)[0]
+        out.append(b)
+    return out

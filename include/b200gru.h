@@ -1,0 +1,158 @@
+/*
+ * b200gru.h — C ABI of the native library behind gru_mpi_cuda_b200.
+ *
+ * One shared object (gru_mpi_cuda_b200/lib/libb200gru.so) is built in-tree with
+ * nvcc for sm_100a and loaded from Python with ctypes.  Every function returns
+ * 0 on success and a negative b200gru_status on failure; b200gru_last_error()
+ * gives the message for the calling thread.  Device pointers are plain
+ * `void*` obtained from `torch.Tensor.data_ptr()`; streams are `cudaStream_t`
+ * passed as `void*` (0 = legacy default stream).
+ *
+ * Citations of the form `ref:NNN` point into /root/reference/namegensf.cu.
+ */
+#ifndef B200GRU_H_
+#define B200GRU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200GRU_MAX_LAYERS 4
+
+typedef enum b200gru_status {
+  B200GRU_OK = 0,
+  B200GRU_ERR_ARG = -1,     /* bad argument / unsupported shape */
+  B200GRU_ERR_IO = -2,      /* file could not be read / written */
+  B200GRU_ERR_CUDA = -3,    /* a CUDA runtime / driver call failed */
+  B200GRU_ERR_STATE = -4    /* call sequence error (e.g. generate before init) */
+} b200gru_status;
+
+/* Model shape.  The reference fixes these as compile-time macros in the
+ * unshipped namegen.h (ref:375-407 uses them); here they are runtime values. */
+typedef struct b200gru_config {
+  int32_t num_char;    /* NUM_CHAR      (default 256)  */
+  int32_t emb_dim;     /* EMBEDDING_DIM (default 512)  */
+  int32_t hidden;      /* HIDDEN_DIM    (default 1024) */
+  int32_t num_layers;  /* stacked GRU layers (reference: 2) */
+  int32_t max_len;     /* MAX_LEN       (default 10)   */
+  int32_t sos;         /* SOS char id   (default 0)    */
+  int32_t eos;         /* EOS char id   (default 1)    */
+} b200gru_config;
+
+const char *b200gru_last_error(void);
+const char *b200gru_version(void);
+
+/* ---------------------------------------------------------------- weights */
+/* Parameter-file layout (ref:375-407): headerless little-endian fp32, tensors
+ * in OFFSETk order: embedding, W_i{r,z,n} per layer, W_h{r,z,n} per layer,
+ * b_i{r,z,n} per layer, b_h{r,z,n} per layer, W_fc, b_fc.
+ * n_tensors = 3 + 12*num_layers (27 for the reference's two layers). */
+int b200gru_num_tensors(const b200gru_config *cfg);
+int64_t b200gru_param_count(const b200gru_config *cfg);
+/* offsets/sizes in floats, rows/cols per tensor (cols = 1 for biases); arrays
+ * must hold b200gru_num_tensors(cfg) entries. */
+int b200gru_param_layout(const b200gru_config *cfg, int64_t *offsets,
+                         int64_t *sizes, int32_t *rows, int32_t *cols);
+/* Name of tensor k ("character_embedding", "W_ir0", ...), static storage. */
+const char *b200gru_tensor_name(const b200gru_config *cfg, int k);
+/* read_binary() equivalent (ref:370-372): whole file into a malloc'd buffer. */
+int b200gru_read_binary(const char *path, void **out_buf, size_t *out_bytes);
+int b200gru_write_binary(const char *path, const void *buf, size_t bytes);
+void b200gru_free_host(void *p);
+/* Deterministic random-init weights, uniform(-1/sqrt(H), 1/sqrt(H)) like
+ * torch.nn.GRU's default init (splitmix64 stream; same bytes on every host). */
+int b200gru_random_init(const b200gru_config *cfg, uint64_t seed, float *out,
+                        int64_t n_floats);
+/* N*max_len uniform floats in [0,1) — stands in for the unshipped main.cpp's
+ * generator (ref:620-626). */
+int b200gru_random_floats(uint64_t seed, float *out, int64_t n);
+
+/* -------------------------------------------------------------- partition */
+/* Static block split of the reference (ref:628-630): jpp = N / size, rank owns
+ * [jpp*rank, jpp*rank + jpp); the N % size tail is dropped. */
+void b200gru_partition(int n_names, int world_size, int rank, int *jpp,
+                       int *start, int *end);
+
+/* ----------------------------------------------------------- CPU oracle A */
+/* flags */
+#define B200GRU_ORACLE_LIBM 1u   /* use libm expf/tanhf instead of the shared
+                                    bit-reproducible math (exact_math.h)     */
+/* Inverse-CDF sampler, ref:322-333 (strict '>' and n-1 fallback). */
+int b200gru_random_select(const float *probs, int n, float r);
+/* Full generation on the CPU in the reference's association order
+ * (ref:649-885).  `params` is the whole weight file, `rfloats` is
+ * [n_names*max_len], `output` is [n_names*(max_len+1)] and is zero-filled
+ * first (ref:643).  `logits_out` (optional) receives [n_names*max_len*num_char]
+ * pre-softmax FC outputs (zeros after EOS). */
+int b200gru_oracle_generate(const b200gru_config *cfg, const float *params,
+                            int n_names, const float *rfloats, char *output,
+                            float *logits_out, uint32_t flags);
+/* Individual ops of the reference (ref:112-313), for unit tests. */
+int b200gru_oracle_matvec(const float *w, const float *x, float *y, int n,
+                          int k);
+int b200gru_oracle_softmax(const float *x, float *y, int n, uint32_t flags);
+int b200gru_oracle_gru_cell(const float *w_ih, const float *w_hh,
+                            const float *b_ih, const float *b_hh,
+                            const float *x, float *h, int in_dim, int hidden,
+                            uint32_t flags);
+
+/* ----------------------------------------------------------- device model */
+typedef struct b200gru_model b200gru_model; /* opaque */
+
+/* precision / kernel family */
+#define B200GRU_MODE_EXACT 0 /* fp32 SIMT, bit-identical to oracle A           */
+#define B200GRU_MODE_TC 1    /* bf16 tcgen05/TMEM/TMA, fp32 accumulate         */
+
+/* namegen_initialize() equivalent (ref:359-618): upload + repack on `device`.
+ * `params` is the host weight file contents.  `max_batch` bounds the names a
+ * single generate() call may run per rank (activation buffers are sized once,
+ * ref:409-468, 583-612). */
+int b200gru_model_create(const b200gru_config *cfg, const float *params,
+                         int device, int max_batch, b200gru_model **out);
+/* namegen_finalize() equivalent (ref:897-1033). */
+int b200gru_model_destroy(b200gru_model *m);
+int64_t b200gru_model_device_bytes(const b200gru_model *m);
+
+/* Where a generate call gets its random floats and puts its characters.  All
+ * pointers are device addresses and may be peer (NVLink-mapped) addresses:
+ * that is how the reference's MPI_Scatter (ref:636) and MPI_Gather (ref:889)
+ * are folded into the kernels.  `rfloats` points at this rank's first float
+ * (root buffer + start*max_len), `output` at this rank's first row
+ * (root buffer + start*(max_len+1)).  If `done_flag` is non-null the last
+ * kernel release-stores `done_value` to it (system scope) after its output
+ * rows are written. */
+typedef struct b200gru_io {
+  const float *rfloats;
+  char *output;
+  uint32_t *done_flag;
+  uint32_t done_value;
+} b200gru_io;
+
+/* namegen() equivalent for one rank's slice (ref:627-890, minus the MPI
+ * calls): generate `n` names.  Asynchronous on `stream`. */
+int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
+                     void *stream);
+/* Number of kernel launches the last b200gru_generate() issued. */
+int b200gru_last_launch_count(const b200gru_model *m);
+/* Debug taps: copy the model's last-step logits [n, num_char] (fp32). */
+int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
+                         void *stream);
+
+/* Kernel that spins (ld.acquire.sys) until flags[i] == value for all i<n;
+ * rank 0 runs it after its own generate to complete the gather. */
+int b200gru_wait_flags(const uint32_t *flags, int n, uint32_t value,
+                       void *stream);
+
+/* ------------------------------------------------- stand-alone device ops */
+/* D[M,N] (fp32) = A[M,K] (bf16, row-major) x B[N,K]^T (bf16, row-major) on
+ * tcgen05; used by tests to validate descriptors / TMA / TMEM plumbing. */
+int b200gru_gemm_bf16_tn(const void *a, const void *b, float *d, int m, int n,
+                         int k, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GRU_H_ */
