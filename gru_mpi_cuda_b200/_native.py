@@ -53,6 +53,14 @@ def _declare(lib):
         "b200gru_last_launch_count": (c_int, [c_void_p]),
         "b200gru_debug_logits": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
         "b200gru_wait_flags": (c_int, [c_void_p, c_int, c_uint32, c_void_p]),
+        "b200gru_symm_alloc": (c_int, [c_int, c_size_t, P(c_void_p), c_void_p]),
+        "b200gru_symm_open": (c_int, [c_int, c_void_p, P(c_void_p)]),
+        "b200gru_symm_close": (c_int, [c_int, c_void_p]),
+        "b200gru_symm_free": (c_int, [c_int, c_void_p]),
+        "b200gru_memcpy_async": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_void_p]),
+        "b200gru_memset_async": (c_int, [c_void_p, c_int, c_size_t, c_void_p]),
+        "b200gru_signal_flag": (c_int, [c_void_p, c_uint32, c_void_p]),
+        "b200gru_can_access_peer": (c_int, [c_int, c_int]),
         "b200gru_gemm_bf16_tn": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     }
     for name, (res, args) in sig.items():

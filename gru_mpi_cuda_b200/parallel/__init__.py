@@ -1,1 +1,11 @@
 from .partition import Slice, partition, rank_info  # noqa: F401
+
+
+def __getattr__(name):  # lazy: dp/symm import torch.distributed
+    if name == "DPContext":
+        from .dp import DPContext
+        return DPContext
+    if name == "SymmBuffer":
+        from .symm import SymmBuffer
+        return SymmBuffer
+    raise AttributeError(name)

@@ -146,6 +146,23 @@ int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
 int b200gru_wait_flags(const uint32_t *flags, int n, uint32_t value,
                        void *stream);
 
+/* ------------------------------------------- peer-visible buffers (NVLink) */
+/* cudaMalloc + zero + CUDA IPC handle (64 bytes).  Stands in for the host
+ * staging buffers of MPI_Scatter / MPI_Gather (ref:632-636, :889): peers map
+ * the buffer and kernels load/store it directly. */
+int b200gru_symm_alloc(int device, size_t bytes, void **ptr,
+                       unsigned char *handle64);
+int b200gru_symm_open(int device, const unsigned char *handle64, void **ptr);
+int b200gru_symm_close(int device, void *ptr);
+int b200gru_symm_free(int device, void *ptr);
+/* kind: 1 = H2D, 2 = D2H, 3 = D2D */
+int b200gru_memcpy_async(void *dst, const void *src, size_t bytes, int kind,
+                         void *stream);
+int b200gru_memset_async(void *dst, int value, size_t bytes, void *stream);
+/* st.release.sys of `value` to `flag` after prior work on `stream`. */
+int b200gru_signal_flag(uint32_t *flag, uint32_t value, void *stream);
+int b200gru_can_access_peer(int device, int peer);
+
 /* ------------------------------------------------- stand-alone device ops */
 /* D[M,N] (fp32) = A[M,K] (bf16, row-major) x B[N,K]^T (bf16, row-major) on
  * tcgen05; used by tests to validate descriptors / TMA / TMEM plumbing. */
