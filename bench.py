@@ -163,14 +163,16 @@ def run_ours(args):
         comm.generate(gen, n_total, rf_host, to_host=True)
     barrier()
 
-    for _ in range(args.warmup):
-        flush.fill_(1)
-        device_step()
-    barrier()
-    launches_per_step = gen.last_launches
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    with ClockSampler(local) as cs:
+    # the sampler starts before warm-up (nvidia-smi takes ~100 ms to come up); its
+    # summary keeps the samples taken under load
+    with ClockSampler(local, period_ms=20) as cs:
+        time.sleep(0.3)
+        for _ in range(args.warmup):
+            flush.fill_(1)
+            device_step()
         barrier()
+        launches_per_step = gen.last_launches
         t_wall0 = time.perf_counter()
         for a, b in evs:
             flush.fill_(2)          # evict L2 between timed iterations (outside the event pair)

@@ -194,6 +194,29 @@ __global__ void exact_sample_kernel(float *__restrict__ logits,
   if (sel == eos) alive[b] = 0;
 }
 
+// One batched GRU layer step with caller-chosen scratch: the two gate GEMMs
+// (ref:676-681 etc.) into scratch, then the elementwise gate sequence
+// (ref:686-763).  scratch holds 2 * batch * 3 * hidden floats.
+int gru_cell_fp32_run(const float *x, const float *h_in, const float *w_ih,
+                      const float *w_hh, const float *b_ih, const float *b_hh,
+                      float *h_out, int batch, int in_dim, int hidden,
+                      float *scratch, cudaStream_t s) {
+  float *g_ih = scratch;
+  float *g_hh = scratch + (size_t)batch * 3 * hidden;
+  if (int rc = exact_sgemm_tn(x, w_ih, g_ih, batch, 3 * hidden, in_dim, s))
+    return rc;
+  if (int rc = exact_sgemm_tn(h_in, w_hh, g_hh, batch, 3 * hidden, hidden, s))
+    return rc;
+  if (h_out != h_in)
+    B200_CUDA(cudaMemcpyAsync(h_out, h_in, sizeof(float) * (size_t)batch * hidden,
+                              cudaMemcpyDeviceToDevice, s));
+  size_t tot = (size_t)batch * hidden;
+  exact_gates_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(
+      nullptr, nullptr, g_ih, g_hh, b_ih, b_hh, h_out, batch, hidden);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 __global__ void signal_done_kernel(uint32_t *flag, uint32_t value) {
   __threadfence_system();
   sm100::st_release_sys(flag, value);
@@ -250,3 +273,27 @@ int exact_generate(b200gru_model *m, int n, const b200gru_io *io,
 }
 
 }  // namespace b200gru
+
+// Stand-alone op: one GRU layer step for a batch, fp32, reference association
+// order (bit-identical to b200gru_oracle_gru_cell per row).  The two GEMM
+// outputs need 2*batch*3*hidden floats of scratch, allocated here per call.
+extern "C" int b200gru_gru_cell_fp32(const float *x, const float *h_in,
+                                     const float *w_ih, const float *w_hh,
+                                     const float *b_ih, const float *b_hh,
+                                     float *h_out, int batch, int in_dim,
+                                     int hidden, void *stream) {
+  using namespace b200gru;
+  B200_REQUIRE(x && h_in && w_ih && w_hh && b_ih && b_hh && h_out, "null argument");
+  B200_REQUIRE(batch > 0 && in_dim > 0 && hidden > 0, "bad dims");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  float *scratch = nullptr;
+  B200_CUDA(cudaMalloc(&scratch, sizeof(float) * 2 * (size_t)batch * 3 * hidden));
+  int rc = gru_cell_fp32_run(x, h_in, w_ih, w_hh, b_ih, b_hh, h_out, batch,
+                             in_dim, hidden, scratch, s);
+  cudaError_t e = cudaStreamSynchronize(s);
+  cudaFree(scratch);
+  if (rc) return rc;
+  if (e != cudaSuccess)
+    return fail(B200GRU_ERR_CUDA, "gru_cell_fp32: %s", cudaGetErrorString(e));
+  return 0;
+}

@@ -68,6 +68,10 @@ int exact_sgemm_tn(const float *a, const float *w, float *c, int m, int n,
                    int k, cudaStream_t s);
 int exact_generate(b200gru_model *m, int n, const b200gru_io *io,
                    cudaStream_t s);
+int gru_cell_fp32_run(const float *x, const float *h_in, const float *w_ih,
+                      const float *w_hh, const float *b_ih, const float *b_hh,
+                      float *h_out, int batch, int in_dim, int hidden,
+                      float *scratch, cudaStream_t s);
 // tensor-core path (gru_tc_sm100.cu)
 int tc_prepare(b200gru_model *m);
 int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s);

@@ -169,6 +169,17 @@ int b200gru_can_access_peer(int device, int peer);
 int b200gru_gemm_bf16_tn(const void *a, const void *b, float *d, int m, int n,
                          int k, void *stream);
 
+/* One GRU layer step for a batch in fp32, the reference's association order
+ * (ref:671-763): h_out[b] = GRUCell(x[b], h_in[b]).  x [batch,in_dim],
+ * h_* [batch,hidden], w_ih [3*hidden,in_dim], w_hh [3*hidden,hidden] with the
+ * r,z,n blocks stacked, b_* [3*hidden]; all device pointers.  Allocates (and
+ * frees) 2*batch*3*hidden floats of scratch for the two GEMM outputs, and
+ * synchronises `stream` before returning. */
+int b200gru_gru_cell_fp32(const float *x, const float *h_in, const float *w_ih,
+                          const float *w_hh, const float *b_ih,
+                          const float *b_hh, float *h_out, int batch,
+                          int in_dim, int hidden, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
