@@ -180,6 +180,23 @@ int b200gru_gru_cell_fp32(const float *x, const float *h_in, const float *w_ih,
                           const float *b_hh, float *h_out, int batch,
                           int in_dim, int hidden, void *stream);
 
+/* Same op for callers that cannot allocate device memory at call time (all of
+ * HBM already belongs to another pool, or cudaMalloc's device-wide sync is not
+ * acceptable in the loop).  No counterpart in the reference.  The GEMM scratch
+ * lives in a fixed B200GRU_NOALLOC_SCRATCH_BYTES array inside the library
+ * image (resident on every GPU that loads it, until exit), so:
+ *   - 2*batch*3*hidden*4 bytes must fit, else B200GRU_ERR_ARG with a message;
+ *   - all calls on one GPU share the array: calls that may overlap there race;
+ *   - the first call on a device resolves the array's address; make it during
+ *     set-up, before any stream capture.
+ * Asynchronous on `stream`; inputs and outputs are the caller's, as above. */
+#define B200GRU_NOALLOC_SCRATCH_BYTES (4u << 20)
+int b200gru_gru_cell_fp32_noalloc(const float *x, const float *h_in,
+                                  const float *w_ih, const float *w_hh,
+                                  const float *b_ih, const float *b_hh,
+                                  float *h_out, int batch, int in_dim,
+                                  int hidden, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
