@@ -1,0 +1,76 @@
+"""Worker for the multi-process tests; launched by torchrun / mp.spawn.
+
+modes:
+  cpu   — gloo, CPU oracle as the generator: checks scatter/gather semantics
+  gpu   — nccl + CUDA IPC: in-kernel P2P scatter/gather vs single-rank result
+"""
+import os
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+import torch
+import torch.distributed as dist
+
+
+def run_cpu(n_names: int):
+    from gru_mpi_cuda_b200 import GRUConfig
+    from gru_mpi_cuda_b200.models import oracle
+    from gru_mpi_cuda_b200.parallel.cpu_dp import generate_cpu
+    from gru_mpi_cuda_b200.utils import weights as W
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    cfg = GRUConfig.tiny()
+    params = W.random_init(cfg, 11)
+    rf = W.random_floats(n_names * cfg.max_len, 5) if rank == 0 else None
+    out = generate_cpu(cfg, params, n_names, rf)
+    if rank == 0:
+        full = oracle.generate(cfg, params, W.random_floats(n_names * cfg.max_len, 5))
+        covered = (n_names // world) * world
+        assert torch.equal(out[:covered], full[:covered]), "rows differ from single-rank result"
+        assert (out[covered:] == 0).all(), "dropped remainder rows must stay zero"
+        print(f"CPU_DP_OK world={world} n={n_names} covered={covered}")
+    else:
+        assert out is None
+    dist.destroy_process_group()
+
+
+def run_gpu(n_names: int, method: str):
+    from gru_mpi_cuda_b200 import GRUConfig
+    from gru_mpi_cuda_b200.models import NameGenerator
+    from gru_mpi_cuda_b200.parallel.dp import DPContext
+    from gru_mpi_cuda_b200.utils import weights as W
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    cfg = GRUConfig.tiny()
+    params = W.random_init(cfg, 11)
+    rf = W.random_floats(n_names * cfg.max_len, 5)
+    for mode in ("exact", "tc"):
+        gen = NameGenerator(cfg, params, device=local, max_batch=n_names, mode=mode)
+        comm = DPContext(cfg, local, n_names, method=method)
+        gen.comm = comm
+        for it in range(3):     # epochs reuse the flags
+            out = gen.generate(n_names, rf if rank == 0 else None)
+        gen.comm = None
+        if rank == 0:
+            single = gen.generate(n_names, rf)
+            covered = (n_names // world) * world
+            assert torch.equal(out[:covered], single[:covered]), f"{mode}: DP rows differ from 1-rank rows"
+            assert (out[covered:] == 0).all()
+            print(f"GPU_DP_OK mode={mode} method={method} world={world} n={n_names}")
+        dist.barrier()
+        comm.close()
+        gen.finalize()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    mode = sys.argv[1]
+    n = int(sys.argv[2])
+    if mode == "cpu":
+        run_cpu(n)
+    else:
+        run_gpu(n, sys.argv[3] if len(sys.argv) > 3 else "p2p")
