@@ -164,6 +164,12 @@ int b200gru_last_launch_count(const b200gru_model *m) {
   return m ? m->last_launches : 0;
 }
 
+int b200gru_model_set_debug(b200gru_model *m, int logits_tap) {
+  B200_REQUIRE(m, "null model");
+  m->debug_logits = logits_tap != 0;
+  return 0;
+}
+
 int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
                          void *stream) {
   B200_REQUIRE(m && dst_device && n >= 0 && n <= m->bpad, "bad arguments");

@@ -4,109 +4,104 @@
 // What the reference does per character of ONE name — 13 matvec launches,
 // 34 elementwise launches, 2 softmax launches, a D2H copy and a CPU sampler
 // (ref:664-878) — becomes, for ALL of a rank's names at once, one launch per
-// GRU layer plus one for FC+softmax+sample:
+// GRU layer plus one for FC+softmax+sample.
 //
-//   layer 0 :  acc[128 names, (r|z|n) x 64 units] = h0 . W_hh0^T      (UMMA)
-//              + gather of T0[char] (= W_ih0.emb[char] + biases, folded at
-//              init; replaces ref:669,:676,:702,:729) -> gates -> h0'
-//   layer l :  acc[.., r|z|n_i] = x . W_ih^T ; acc[.., r|z] += h . W_hh^T ;
-//              acc[.., n_h] = h . W_hn^T  -> gates -> h'  (ref:770-854)
-//   FC      :  acc[128 names, C] = h_top . W_fc^T -> +b_fc -> softmax (full sum,
-//              no max subtraction, ref:302-313) -> inverse-CDF walk in index
-//              order with strict '>' (ref:322-333) -> output byte + next char.
+// Every GRU layer is the same fused GEMM + gate kernel (gru_layer_kernel):
 //
-// Kernel anatomy (one CTA per SM, persistent over tiles, 256 threads):
-//   warp 0   TMA producer   cp.async.bulk.tensor -> 128B-swizzled smem ring
-//   warp 1   MMA issuer     tcgen05.mma kind::f16, M=128, N in {192,128,64,C}
-//   warp 2   TMEM allocator 512 columns = 2 accumulator stages of 256
-//   warp 4-7 epilogue       tcgen05.ld -> gate math in registers -> global
+//   acc[128 names, 256 cols] per 64-unit block, columns [ n_i | r | z | n_h ]
+//     x-part : [n_i|r|z] (cols   0..191)  = x . Wx^T   one UMMA N=192 per k16
+//     h-part : [r|z|n_h] (cols  64..255) += h . Wh^T   one UMMA N=192 per k16
+//   r and z receive both halves in the same TMEM columns; n_i and n_h stay
+//   apart because r multiplies only the recurrent half (ref:739-744).  The
+//   n_h columns are zeroed (tcgen05.st) by the epilogue when it hands a TMEM
+//   stage back, so every recurrent MMA can simply accumulate.
+//   epilogue: r = s(acc_r + b_r), z = s(acc_z + b_z),
+//             n = tanh(acc_ni + b_in + r * (acc_nh + b_hn)), h' = n + z (h - n)
+//
+//   layer 0: x is the ONE-HOT row of the current character and Wx is the table
+//            T0[c] = W_i*0 . emb[c] + biases (computed once at init), so the
+//            embedding lookup and the three input matvecs (ref:669, :676,
+//            :702, :729) ride the tensor core as K = NUM_CHAR extra columns
+//            instead of being gathered per thread.
+//   layer l: x is the layer below's fresh hidden state (ref:773, :797, :821).
+//
+// FC (fc_sample_kernel): acc[128 names, C] = h_top . W_fc^T, then per name
+// +b_fc, exp, full sum (no max subtraction, ref:302-313), inverse-CDF walk in
+// index order with strict '>' and C-1 fallback (ref:322-333), output byte,
+// next-step one-hot row, EOS bookkeeping (ref:876-882).
+//
+// Kernel anatomy (one CTA per SM, persistent over tiles):
+//   warp 0    TMA producer   cp.async.bulk.tensor -> 128B-swizzled smem ring
+//   warp 1    MMA issuer     tcgen05.mma kind::f16, M=128
+//   warp 2    TMEM allocator 512 columns = 2 accumulator stages of 256
+//   warp 4..  epilogue       tcgen05.ld -> gate math in registers -> global
 // The accumulator is double-buffered in TMEM so the epilogue of tile i
 // overlaps the MMAs of tile i+1.
-//
-// Weights are repacked once at init so that a 64-unit block's r, z and n rows
-// are contiguous: one TMA box / one UMMA covers all three gates and the gate
-// math for a (name, unit) pair is local to one thread.
 #include "model.hpp"
 #include "sm100_ptx.cuh"
 
 namespace b200gru {
 using namespace sm100;
 
-enum : int { MODE_L0 = 0, MODE_LN = 1, MODE_FC = 2 };
-
-constexpr int TC_THREADS = 256;
 constexpr int TC_BLOCK_K = 64;               // 128 bytes of bf16 per row
 constexpr int TC_A_BYTES = kTileM * 128;     // 16 KB
 constexpr int TC_TMEM_COLS = 512;
 constexpr int TC_ACC_STRIDE = 256;           // TMEM columns per accumulator
 
-struct TcArgs {
+// ------------------------------------------------------------------ layers
+constexpr int L_EPI_WARPS = 8;
+constexpr int L_THREADS = (4 + L_EPI_WARPS) * 32;
+constexpr int L_B_BYTES = 192 * 128;         // 24 KB
+constexpr int L_STAGE_BYTES = TC_A_BYTES + L_B_BYTES;
+constexpr int L_STAGES = 5;
+constexpr int L_SMEM_BYTES = L_STAGES * L_STAGE_BYTES + 1024 + 256;
+
+struct LayerArgs {
   int n;            // valid names (rows)
   int m_tiles;      // ceil(n / 128)
-  int n_blocks;     // H / 64 (1 for FC)
-  int kb_x;         // k-blocks (of 64) of the x operand  (0: none)
-  int kb_h;         // k-blocks of the recurrent operand  (0: h == 0, step 0)
-  int H, C, T, step, eos;
-  const float *t0;          // [C, H/64, 3, 64]           (L0)
-  const float *bias;        // [H/64, 4, 64]              (L0: only q=3, LN: all)
-  const int32_t *chars;     // [bpad]                     (L0 gather index)
+  int n_blocks;     // H / 64
+  int kb_x;         // k-blocks (of 64) of the x operand
+  int kb_h;         // k-blocks of the recurrent operand (0: h == 0, step 0)
+  int H;
+  const float *bias;            // [H/64, 4, 64]: b_in, b_r, b_z, b_hn
   const __nv_bfloat16 *h_prev;  // [bpad, H]
   __nv_bfloat16 *h_out;         // [bpad, H]
-  // FC
-  const float *b_fc;
-  float *logits;            // optional [bpad, C] tap
-  const float *rfloats;     // [n, T]   (may be a peer address)
-  char *output;             // [n, T+1] (may be a peer address)
-  int32_t *chars_out;
-  uint8_t *alive;
 };
 
-template <int MODE>
-struct TcCfg {
-  static constexpr int B_ROWS_MAX = (MODE == MODE_FC) ? 256 : 192;
-  static constexpr int B_BYTES_MAX = B_ROWS_MAX * 128;
-  static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES_MAX;
-  static constexpr int STAGES = (MODE == MODE_FC) ? 4 : 5;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256;
-};
-
-template <int MODE>
-__global__ void __launch_bounds__(TC_THREADS, 1)
-gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
-              const __grid_constant__ CUtensorMap map_h,
-              const __grid_constant__ CUtensorMap map_wx,
-              const __grid_constant__ CUtensorMap map_wh, const TcArgs args) {
-  using Cfg = TcCfg<MODE>;
-  constexpr int STAGES = Cfg::STAGES;
+__global__ void __launch_bounds__(L_THREADS, 1)
+gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
+                 const __grid_constant__ CUtensorMap map_h,
+                 const __grid_constant__ CUtensorMap map_wx,
+                 const __grid_constant__ CUtensorMap map_wh,
+                 const LayerArgs args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * Cfg::STAGE_BYTES);
-  uint64_t *full_bar = bars;                  // [STAGES]
-  uint64_t *empty_bar = bars + STAGES;        // [STAGES]
-  uint64_t *tmem_full = bars + 2 * STAGES;    // [2]
-  uint64_t *tmem_empty = bars + 2 * STAGES + 2;  // [2]
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 4);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L_STAGES * L_STAGE_BYTES);
+  uint64_t *full_bar = bars;                       // [STAGES]
+  uint64_t *empty_bar = bars + L_STAGES;           // [STAGES]
+  uint64_t *tmem_full = bars + 2 * L_STAGES;       // [2]
+  uint64_t *tmem_empty = bars + 2 * L_STAGES + 2;  // [2]
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * L_STAGES + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = args.m_tiles * args.n_blocks;
-  const int b_rows = (MODE == MODE_FC) ? args.C : 192;
-  const uint32_t b_bytes = (uint32_t)b_rows * 128u;
   const int kb_total = args.kb_x + args.kb_h;
 
   if (warp == 0 && lane == 0) {
-    if (args.kb_x) { tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_wx); }
+    tma_prefetch_desc(&map_x);
+    tma_prefetch_desc(&map_wx);
     if (args.kb_h) { tma_prefetch_desc(&map_h); tma_prefetch_desc(&map_wh); }
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < STAGES; ++i) {
+    for (int i = 0; i < L_STAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+      mbar_init(&tmem_empty[i], L_EPI_WARPS);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -115,6 +110,26 @@ gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+
+  // The n_h columns of both accumulator stages start at zero (the recurrent
+  // MMAs only ever accumulate into them); later the epilogue re-zeroes them
+  // each time it hands a stage back.
+  if (warp >= 4) {
+    const uint32_t lane_base0 = (uint32_t)((warp & 3) * 32) << 16;
+    const int half0 = (warp - 4) >> 2;
+    uint32_t zero[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) zero[i] = 0u;
+#pragma unroll
+    for (int st = 0; st < 2; ++st)
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+        tmem_st16(tmem_base + lane_base0 + st * TC_ACC_STRIDE + 192 + half0 * 32 + c * 16, zero);
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
 
   if (warp == 0) {
     // ===================================================== TMA producer
@@ -126,16 +141,16 @@ gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
         const int n_blk = tile % args.n_blocks;
         for (int kb = 0; kb < kb_total; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t *sa = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t *sa = smem + stage * L_STAGE_BYTES;
           uint8_t *sb = sa + TC_A_BYTES;
-          mbar_expect_tx(&full_bar[stage], TC_A_BYTES + b_bytes);
+          mbar_expect_tx(&full_bar[stage], TC_A_BYTES + L_B_BYTES);
           const bool is_x = kb < args.kb_x;
           const int k = (is_x ? kb : kb - args.kb_x) * TC_BLOCK_K;
           tma_load_2d(sa, is_x ? &map_x : &map_h, &full_bar[stage], k,
                       m_tile * kTileM);
           tma_load_2d(sb, is_x ? &map_wx : &map_wh, &full_bar[stage], k,
-                      n_blk * b_rows);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                      n_blk * 192);
+          if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -146,9 +161,7 @@ gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
       uint32_t phase = 0;
       int acc_stage = 0;
       uint32_t acc_phase = 0;
-      const uint32_t idesc_full = umma_idesc_bf16(kTileM, (uint32_t)b_rows);
-      const uint32_t idesc_rz = umma_idesc_bf16(kTileM, 128);
-      const uint32_t idesc_n = umma_idesc_bf16(kTileM, 64);
+      const uint32_t idesc = umma_idesc_bf16(kTileM, 192);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
         tc_fence_after();
@@ -156,30 +169,20 @@ gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
         for (int kb = 0; kb < kb_total; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-          const uint32_t sb = sa + TC_A_BYTES;
+          const uint32_t sa = smem_u32(smem + stage * L_STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(sa);
-          const uint64_t db = umma_desc_sw128(sb);
+          const uint64_t db = umma_desc_sw128(sa + TC_A_BYTES);
           const bool is_x = kb < args.kb_x;
-          const int kh = kb - args.kb_x;
 #pragma unroll
           for (int k = 0; k < TC_BLOCK_K / 16; ++k) {
             const uint64_t koff = (uint64_t)(k * 32 >> 4);  // 32 B per UMMA_K
-            if (MODE != MODE_LN || is_x) {
-              // one MMA over every gate column of this unit block
-              umma_bf16(d, da + koff, db + koff, idesc_full,
-                        (kb | k) != 0 ? 1u : 0u);
-            } else {
-              // recurrent half of a stacked layer: r,z accumulate onto the
-              // x-projection, n_h goes to its own columns (r multiplies it)
-              umma_bf16(d, da + koff, db + koff, idesc_rz,
-                        (args.kb_x | kh | k) != 0 ? 1u : 0u);
-              umma_bf16(d + 192, da + koff, db + koff + (128 * 128 >> 4),
-                        idesc_n, (kh | k) != 0 ? 1u : 0u);
-            }
+            if (is_x)  // [n_i | r | z]: the tile's first MMA overwrites
+              umma_bf16(d, da + koff, db + koff, idesc, (kb | k) != 0 ? 1u : 0u);
+            else       // [r | z | n_h]: always accumulates (n_h pre-zeroed)
+              umma_bf16(d + 64, da + koff, db + koff, idesc, 1u);
           }
           umma_commit(&empty_bar[stage]);  // smem slot free when MMAs retire
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
         }
         umma_commit(&tmem_full[acc_stage]);  // accumulator ready
         if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
@@ -187,7 +190,11 @@ gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
     }
   } else if (warp >= 4) {
     // ========================================================= epilogue
-    const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
+    // 8 warps: warp%4 picks the TMEM lane quarter (hardware rule), warp/4
+    // picks which 32 of the tile's 64 units this warp handles.
+    const int quarter = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     int acc_stage = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -195,144 +202,80 @@ gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
       const int n_blk = tile % args.n_blocks;
       const int row = m_tile * kTileM + quarter * 32 + lane;
       const bool valid = row < args.n;
+      const bool has_h = args.kb_h > 0;
+      const size_t hoff = (size_t)row * args.H + (size_t)n_blk * 64 + half * 32;
+      // previous hidden for this thread's 32 units: issue the loads before
+      // waiting on the accumulator so their latency hides behind the MMAs
+      uint4 hq[4];
+      if (has_h) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(args.h_prev + hoff);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hq[i] = src[i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hq[i] = make_uint4(0, 0, 0, 0);
+      }
+      const float4 *bias4 =
+          reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
+
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
-      const uint32_t t =
-          tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * TC_ACC_STRIDE;
-
-      if constexpr (MODE == MODE_L0 || MODE == MODE_LN) {
-        const bool has_acc = kb_total > 0;
-        const bool has_h = args.kb_h > 0;
-        const float *bias = args.bias + (size_t)n_blk * 4 * 64;
-        const float *t0row = nullptr;
-        if (MODE == MODE_L0)
-          t0row = args.t0 +
-                  ((size_t)args.chars[row] * args.n_blocks + n_blk) * 3 * 64;
-        const size_t hoff = (size_t)row * args.H + (size_t)n_blk * 64;
-#pragma unroll 1
-        for (int ch = 0; ch < 4; ++ch) {
-          uint32_t vr[16], vz[16], vn[16], vh[16];
-          if (has_acc) {
-            tmem_ld16(t + ch * 16, vr);
-            tmem_ld16(t + 64 + ch * 16, vz);
-            tmem_ld16(t + 128 + ch * 16, vn);
-            if (MODE == MODE_LN && has_h) tmem_ld16(t + 192 + ch * 16, vh);
-            tmem_ld_wait();
-          }
-          if (!has_acc) {
+      const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
 #pragma unroll
-            for (int i = 0; i < 16; ++i) vr[i] = vz[i] = vn[i] = 0u;
-          }
-          if (!(MODE == MODE_LN && has_h)) {
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t vn[16], vr[16], vz[16], vh[16];
+        tmem_ld16(t + ch * 16, vn);
+        tmem_ld16(t + 64 + ch * 16, vr);
+        tmem_ld16(t + 128 + ch * 16, vz);
+        tmem_ld16(t + 192 + ch * 16, vh);
+        tmem_ld_wait();
+        const uint32_t hw[8] = {hq[2 * ch].x,     hq[2 * ch].y,     hq[2 * ch].z,
+                                hq[2 * ch].w,     hq[2 * ch + 1].x, hq[2 * ch + 1].y,
+                                hq[2 * ch + 1].z, hq[2 * ch + 1].w};
+        uint32_t packed[8];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) vh[i] = 0u;
-          }
-          // previous hidden, 16 bf16 = 32 bytes
-          float hp[16];
-          if (has_h) {
-            const uint4 *src =
-                reinterpret_cast<const uint4 *>(args.h_prev + hoff + ch * 16);
-            uint4 q0 = src[0], q1 = src[1];
-            const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        for (int q = 0; q < 4; ++q) {  // 4 units per float4 of bias
+          const float4 b_in = __ldg(bias4 + ch * 4 + q);
+          const float4 b_r = __ldg(bias4 + 16 + ch * 4 + q);
+          const float4 b_z = __ldg(bias4 + 32 + ch * 4 + q);
+          const float4 b_hn = __ldg(bias4 + 48 + ch * 4 + q);
+          const float bi[4] = {b_in.x, b_in.y, b_in.z, b_in.w};
+          const float br[4] = {b_r.x, b_r.y, b_r.z, b_r.w};
+          const float bz[4] = {b_z.x, b_z.y, b_z.z, b_z.w};
+          const float bh[4] = {b_hn.x, b_hn.y, b_hn.z, b_hn.w};
+          float hn[4];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              hp[2 * i] = __uint_as_float(w[i] << 16);
-              hp[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
-            }
-          } else {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) hp[i] = 0.0f;
+          for (int e = 0; e < 4; ++e) {
+            const int i = q * 4 + e;
+            const uint32_t w = hw[i >> 1];
+            const float hp = __uint_as_float((i & 1) ? (w & 0xFFFF0000u) : (w << 16));
+            const float r = sigmoid_approx(__uint_as_float(vr[i]) + br[e]);
+            const float z = sigmoid_approx(__uint_as_float(vz[i]) + bz[e]);
+            const float nn = tanh_approx(fmaf(r, __uint_as_float(vh[i]) + bh[e],
+                                              __uint_as_float(vn[i]) + bi[e]));
+            // h' = (1-z)*n + z*h  ==  n + z*(h - n)     (ref:752-763)
+            hn[e] = fmaf(z, hp - nn, nn);
           }
-          uint32_t packed[8];
-#pragma unroll
-          for (int i = 0; i < 16; i += 2) {
-            float hn[2];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int u = ch * 16 + i + e;
-              float ar = __uint_as_float(vr[i + e]);
-              float az = __uint_as_float(vz[i + e]);
-              float an = __uint_as_float(vn[i + e]);
-              float r, z, nn;
-              if (MODE == MODE_L0) {
-                // T0 already holds W_i.x + b_i (+ b_hr / b_hz)
-                r = sigmoid_approx(ar + __ldg(t0row + u));
-                z = sigmoid_approx(az + __ldg(t0row + 64 + u));
-                nn = tanh_approx(
-                    fmaf(r, an + __ldg(bias + 3 * 64 + u), __ldg(t0row + 128 + u)));
-              } else {
-                float ah = __uint_as_float(vh[i + e]);
-                r = sigmoid_approx(ar + __ldg(bias + u));
-                z = sigmoid_approx(az + __ldg(bias + 64 + u));
-                nn = tanh_approx(fmaf(r, ah + __ldg(bias + 3 * 64 + u),
-                                      an + __ldg(bias + 2 * 64 + u)));
-              }
-              // h' = (1-z)*n + z*h  ==  n + z*(h - n)     (ref:752-763)
-              hn[e] = fmaf(z, hp[i + e] - nn, nn);
-            }
-            __nv_bfloat162 p2 = __floats2bfloat162_rn(hn[0], hn[1]);
-            packed[i / 2] = *reinterpret_cast<uint32_t *>(&p2);
-          }
-          if (valid) {
-            uint4 *dst = reinterpret_cast<uint4 *>(args.h_out + hoff + ch * 16);
-            dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-            dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
-          }
-        }
-      } else {
-        // ---------------------------------- FC + softmax + sample (per name)
-        const int C = args.C;
-        const bool live = valid && args.alive[row] != 0;
-        const float kLog2e = 1.4426950408889634f;
-        float sum = 0.0f;
-#pragma unroll 1
-        for (int c0 = 0; c0 < C; c0 += 16) {
-          uint32_t v[16];
-          tmem_ld16(t + c0, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float x = __uint_as_float(v[i]) + __ldg(args.b_fc + c0 + i);
-            sum += ex2_approx(x * kLog2e);
-            if (args.logits && valid)
-              args.logits[(size_t)row * C + c0 + i] = live ? x : 0.0f;
-          }
-        }
-        const float inv = 1.0f / sum;
-        const float r =
-            live ? args.rfloats[(size_t)row * args.T + args.step] : 2.0f;
-        float psum = 0.0f;
-        int sel = C - 1;
-        bool found = false;
-#pragma unroll 1
-        for (int c0 = 0; c0 < C; c0 += 16) {
-          // warp-uniform early exit once every lane has its character
-          if (__all_sync(0xffffffffu, found || !live)) break;
-          uint32_t v[16];
-          tmem_ld16(t + c0, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float x = __uint_as_float(v[i]) + __ldg(args.b_fc + c0 + i);
-            psum += ex2_approx(x * kLog2e) * inv;
-            if (!found && psum > r) {
-              sel = c0 + i;
-              found = true;
-            }
-          }
+          __nv_bfloat162 p0 = __floats2bfloat162_rn(hn[0], hn[1]);
+          __nv_bfloat162 p1 = __floats2bfloat162_rn(hn[2], hn[3]);
+          packed[q * 2] = *reinterpret_cast<uint32_t *>(&p0);
+          packed[q * 2 + 1] = *reinterpret_cast<uint32_t *>(&p1);
         }
         if (valid) {
-          char *orow = args.output + (size_t)row * (args.T + 1);
-          if (args.step == 0)
-            for (int l = 1; l <= args.T; ++l) orow[l] = 0;  // NUL pad, ref:643
-          if (live) {
-            orow[args.step] = (char)sel;  // EOS id is written too, ref:877
-            args.chars_out[row] = sel;
-            if (sel == args.eos) args.alive[row] = 0;  // ref:881
-          }
+          uint4 *dst = reinterpret_cast<uint4 *>(args.h_out + hoff + ch * 16);
+          dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+          dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
         }
       }
-      // accumulator drained: hand the TMEM stage back to the MMA warp
+      // re-zero this warp's n_h columns, then hand the stage back
+      {
+        uint32_t zero[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) zero[i] = 0u;
+        tmem_st16(t + 192, zero);
+        tmem_st16(t + 192 + 16, zero);
+        tmem_st_wait();
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
@@ -348,18 +291,188 @@ gru_tc_kernel(const __grid_constant__ CUtensorMap map_x,
   }
 }
 
+// ---------------------------------------------------------------------- FC
+constexpr int F_THREADS = 256;               // 4 role warps + 4 epilogue warps
+constexpr int F_B_BYTES_MAX = 256 * 128;     // 32 KB
+constexpr int F_STAGE_BYTES = TC_A_BYTES + F_B_BYTES_MAX;
+constexpr int F_STAGES = 4;
+constexpr int F_SMEM_BYTES = F_STAGES * F_STAGE_BYTES + 1024 + 256;
+
+struct FcArgs {
+  int n, m_tiles, kb, H, C, T, step, eos, kx;  // kx = one-hot row length
+  const float *b_fc;
+  float *logits;            // optional [bpad, C] tap (tests / debugging)
+  const float *rfloats;     // [n, T]   (may be a peer address)
+  char *output;             // [n, T+1] (may be a peer address)
+  int32_t *chars;
+  uint8_t *alive;
+  __nv_bfloat16 *onehot;    // [bpad, kx]
+};
+
+__global__ void __launch_bounds__(F_THREADS, 1)
+fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
+                 const __grid_constant__ CUtensorMap map_w, const FcArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + F_STAGES * F_STAGE_BYTES);
+  uint64_t *full_bar = bars, *empty_bar = bars + F_STAGES;
+  uint64_t *tmem_full = bars + 2 * F_STAGES, *tmem_empty = bars + 2 * F_STAGES + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * F_STAGES + 4);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int C = args.C;
+  const uint32_t b_bytes = (uint32_t)C * 128u;
+
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_h); tma_prefetch_desc(&map_w); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < F_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<TC_TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x)
+        for (int kb = 0; kb < args.kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t *sa = smem + stage * F_STAGE_BYTES;
+          mbar_expect_tx(&full_bar[stage], TC_A_BYTES + b_bytes);
+          tma_load_2d(sa, &map_h, &full_bar[stage], kb * TC_BLOCK_K, tile * kTileM);
+          tma_load_2d(sa + TC_A_BYTES, &map_w, &full_bar[stage], kb * TC_BLOCK_K, 0);
+          if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
+        }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0, acc_stage = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)C);
+      for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
+        for (int kb = 0; kb < args.kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * F_STAGE_BYTES);
+          const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + TC_A_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit(&empty_bar[stage]);
+          if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full[acc_stage]);
+        if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    const int quarter = warp & 3;
+    int acc_stage = 0;
+    uint32_t acc_phase = 0;
+    const float kLog2e = 1.4426950408889634f;
+    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x) {
+      const int row = tile * kTileM + quarter * 32 + lane;
+      const bool valid = row < args.n;
+      const bool live = valid && args.alive[row] != 0;
+      // this step's random float: fetched (possibly over NVLink from the root
+      // rank's buffer — the MPI_Scatter of ref:636) before the accumulator wait
+      const float r = live ? args.rfloats[(size_t)row * args.T + args.step] : 2.0f;
+      const int old_char = valid ? args.chars[row] : 0;
+      mbar_wait(&tmem_full[acc_stage], acc_phase);
+      tc_fence_after();
+      const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * TC_ACC_STRIDE;
+      // pass 1: e_i = exp(f_i + b_i), kept in TMEM in place; four partial sums
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < C; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(t + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 b = __ldg(reinterpret_cast<const float4 *>(args.b_fc + c0) + q);
+          const float bb[4] = {b.x, b.y, b.z, b.w};
+          float e[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float x = __uint_as_float(v[q * 4 + j]) + bb[j];
+            if (args.logits && valid) args.logits[(size_t)row * C + c0 + q * 4 + j] = live ? x : 0.0f;
+            e[j] = ex2_approx(x * kLog2e);
+            v[q * 4 + j] = __float_as_uint(e[j]);
+          }
+          s0 += e[0]; s1 += e[1]; s2 += e[2]; s3 += e[3];
+        }
+        tmem_st16(t + c0, v);
+      }
+      tmem_st_wait();
+      const float sum = (s0 + s1) + (s2 + s3);
+      // pass 2: first i with sum_{j<=i} p_j > r, p_j = e_j / sum (ref:322-333)
+      const float inv = 1.0f / sum;
+      float psum = 0.0f;
+      int sel = C - 1;
+      bool found = false;
+#pragma unroll 1
+      for (int c0 = 0; c0 < C; c0 += 16) {
+        if (__all_sync(0xffffffffu, found || !live)) break;  // warp-uniform exit
+        uint32_t v[16];
+        tmem_ld16(t + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          psum = fmaf(__uint_as_float(v[i]), inv, psum);
+          if (!found && psum > r) { sel = c0 + i; found = true; }
+        }
+      }
+      if (valid) {
+        char *orow = args.output + (size_t)row * (args.T + 1);
+        if (args.step == 0)
+          for (int l = 1; l <= args.T; ++l) orow[l] = 0;  // NUL pad, ref:643
+        if (live) {
+          orow[args.step] = (char)sel;  // EOS id is written too, ref:877
+          args.chars[row] = sel;
+          // next step's layer-0 input: move the 1 in this name's one-hot row
+          __nv_bfloat16 *oh = args.onehot + (size_t)row * args.kx;
+          oh[old_char] = __float2bfloat16_rn(0.0f);
+          oh[sel] = __float2bfloat16_rn(1.0f);
+          if (sel == args.eos) args.alive[row] = 0;  // ref:881
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
+      if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<TC_TMEM_COLS>(tmem_base);
+  }
+}
+
 // ------------------------------------------------------------- init / packing
-// fp32 [3][H][K] (gate-stacked, as in the file) -> bf16 [H/64][3][64][K]
+// fp32 [3][H][K] (gate-stacked r,z,n as in the file) -> bf16 [H/64][3][64][K]
+// with the gate order of the packed block given by (g0,g1,g2).
 __global__ void pack_gate_weights_kernel(const float *__restrict__ src,
                                          __nv_bfloat16 *__restrict__ dst, int H,
-                                         int K) {
+                                         int K, int g0, int g1, int g2) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   size_t total = (size_t)3 * H * K;
   if (idx >= total) return;
   int k = (int)(idx % K);
   size_t prow = idx / K;  // packed row
   int jb = (int)(prow / 192), rem = (int)(prow % 192);
-  int g = rem / 64, u = rem % 64;
+  int slot = rem / 64, u = rem % 64;
+  int g = slot == 0 ? g0 : (slot == 1 ? g1 : g2);
   dst[idx] = __float2bfloat16_rn(src[((size_t)g * H + jb * 64 + u) * K + k]);
 }
 
@@ -369,44 +482,59 @@ __global__ void to_bf16_kernel(const float *__restrict__ src,
   if (idx < n) dst[idx] = __float2bfloat16_rn(src[idx]);
 }
 
-// t0_tc[c][jb][g][u] = W_i{g}0 . emb[c] + b_i{g}0 (+ b_h{g}0 for r,z)
+// Layer-0 "x weights": t0w[jb][slot][u][c], slots (n, r, z), K = kx >= C:
+//   W_i{g}0 . emb[c] + b_i{g}0 (+ b_h{g}0 for r, z); zero for c >= C.
 __global__ void pack_t0_kernel(const float *__restrict__ t0_raw,
                                const float *__restrict__ b_ih,
                                const float *__restrict__ b_hh,
-                               float *__restrict__ t0_tc, int C, int H) {
+                               __nv_bfloat16 *__restrict__ t0w, int C, int H,
+                               int kx) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (size_t)C * 3 * H) return;
-  int c = (int)(idx / (3 * H));
-  int rem = (int)(idx % (3 * H));
-  int jb = rem / 192, g = (rem % 192) / 64, u = rem % 64;
+  if (idx >= (size_t)3 * H * kx) return;
+  int c = (int)(idx % kx);
+  size_t prow = idx / kx;
+  int jb = (int)(prow / 192), rem = (int)(prow % 192);
+  int slot = rem / 64, u = rem % 64;
+  int g = slot == 0 ? 2 : slot - 1;  // slots (n, r, z) <- gates (2, 0, 1)
   int i = jb * 64 + u;
-  float v = t0_raw[(size_t)c * 3 * H + g * H + i] + b_ih[g * H + i];
-  if (g < 2) v += b_hh[g * H + i];
-  t0_tc[idx] = v;
+  float v = 0.0f;
+  if (c < C) {
+    v = t0_raw[(size_t)c * 3 * H + g * H + i] + b_ih[g * H + i];
+    if (g < 2) v += b_hh[g * H + i];
+  }
+  t0w[idx] = __float2bfloat16_rn(v);
 }
 
-// bias[jb][q][u]: q=0 b_ir+b_hr, q=1 b_iz+b_hz, q=2 b_in, q=3 b_hn
+// bias[jb][q][u]: q=0 b_in, q=1 b_ir+b_hr, q=2 b_iz+b_hz, q=3 b_hn.
+// Layer 0 folds q=0..2 into the T0 table, so they are zero there.
 __global__ void pack_bias_kernel(const float *__restrict__ b_ih,
                                  const float *__restrict__ b_hh,
-                                 float *__restrict__ out, int H) {
+                                 float *__restrict__ out, int H, int folded) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= 4 * H) return;
   int jb = idx / 256, q = (idx % 256) / 64, u = idx % 64;
   int i = jb * 64 + u;
   float v;
-  if (q == 0) v = b_ih[i] + b_hh[i];
-  else if (q == 1) v = b_ih[H + i] + b_hh[H + i];
-  else if (q == 2) v = b_ih[2 * H + i];
+  if (q == 0) v = folded ? 0.0f : b_ih[2 * H + i];
+  else if (q == 1) v = folded ? 0.0f : b_ih[i] + b_hh[i];
+  else if (q == 2) v = folded ? 0.0f : b_ih[H + i] + b_hh[H + i];
   else v = b_hh[2 * H + i];
   out[idx] = v;
 }
 
-__global__ void tc_init_kernel(int32_t *chars, uint8_t *alive, int n, int bpad,
+// Per-call reset: chars = SOS (ref:652), alive flags, one-hot rows = e_SOS.
+__global__ void tc_init_kernel(int32_t *chars, uint8_t *alive,
+                               __nv_bfloat16 *onehot, int n, int rows, int kx,
                                int sos) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < bpad) {
-    chars[i] = sos;       // ref:652
-    alive[i] = i < n;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)rows * kx;
+  if (idx < total) {
+    int c = (int)(idx % kx);
+    onehot[idx] = __float2bfloat16_rn(c == sos ? 1.0f : 0.0f);
+  }
+  if (idx < (size_t)rows) {
+    chars[idx] = sos;
+    alive[idx] = idx < (size_t)n;
   }
 }
 
@@ -435,55 +563,54 @@ int tc_prepare(b200gru_model *m) {
   LayoutIndex ix(L);
   const unsigned TPB = 256;
   auto blocks = [&](size_t n) { return (unsigned)((n + TPB - 1) / TPB); };
+  const int kx = (C + 63) / 64 * 64;
+  m->kx = kx;
 
-  if (int rc = tc_alloc(m, &m->t0_tc, (size_t)C * 3 * H)) return rc;
-  pack_t0_kernel<<<blocks((size_t)C * 3 * H), TPB>>>(
-      m->t0_raw, m->P(ix.b_i(0, 0)), m->P(ix.b_h(0, 0)), m->t0_tc, C, H);
+  // layer-0 input: one-hot rows and the T0 table as a K-major weight
+  if (int rc = tc_alloc(m, &m->onehot, (size_t)m->bpad * kx)) return rc;
+  B200_CUDA(cudaMemset(m->onehot, 0, sizeof(__nv_bfloat16) * (size_t)m->bpad * kx));
+  if (int rc = make_tmap_bf16_2d(&m->map_onehot, m->onehot, (uint64_t)m->bpad, kx, kTileM, 64))
+    return rc;
+  if (int rc = tc_alloc(m, &m->t0w, (size_t)3 * H * kx)) return rc;
+  pack_t0_kernel<<<blocks((size_t)3 * H * kx), TPB>>>(
+      m->t0_raw, m->P(ix.b_i(0, 0)), m->P(ix.b_h(0, 0)), m->t0w, C, H, kx);
+  if (int rc = make_tmap_bf16_2d(&m->map_t0w, m->t0w, 3 * (uint64_t)H, kx, 192, 64))
+    return rc;
 
   for (int l = 0; l < L; ++l) {
     TcLayer &t = m->tc[l];
     const size_t wn = (size_t)3 * H * H;
     if (l > 0) {
       if (int rc = tc_alloc(m, &t.w_ih, wn)) return rc;
-      pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_i(l, 0)), t.w_ih,
-                                                    H, H);
-      if (int rc = make_tmap_bf16_2d(&t.map_w_ih, t.w_ih, 3 * (uint64_t)H, H,
-                                     192, 64))
+      // x-part column order [n_i | r | z]
+      pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_i(l, 0)), t.w_ih, H, H, 2, 0, 1);
+      if (int rc = make_tmap_bf16_2d(&t.map_w_ih, t.w_ih, 3 * (uint64_t)H, H, 192, 64))
         return rc;
     }
     if (int rc = tc_alloc(m, &t.w_hh, wn)) return rc;
-    pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_h(l, 0)), t.w_hh, H,
-                                                  H);
-    if (int rc =
-            make_tmap_bf16_2d(&t.map_w_hh, t.w_hh, 3 * (uint64_t)H, H, 192, 64))
+    // h-part column order [r | z | n_h]
+    pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_h(l, 0)), t.w_hh, H, H, 0, 1, 2);
+    if (int rc = make_tmap_bf16_2d(&t.map_w_hh, t.w_hh, 3 * (uint64_t)H, H, 192, 64))
       return rc;
     if (int rc = tc_alloc(m, &t.bias, (size_t)4 * H)) return rc;
-    pack_bias_kernel<<<blocks((size_t)4 * H), TPB>>>(
-        m->P(ix.b_i(l, 0)), m->P(ix.b_h(l, 0)), t.bias, H);
+    pack_bias_kernel<<<blocks((size_t)4 * H), TPB>>>(m->P(ix.b_i(l, 0)), m->P(ix.b_h(l, 0)),
+                                                     t.bias, H, l == 0 ? 1 : 0);
     for (int pp = 0; pp < 2; ++pp) {
       if (int rc = tc_alloc(m, &t.h[pp], (size_t)m->bpad * H)) return rc;
       B200_CUDA(cudaMemset(t.h[pp], 0, sizeof(__nv_bfloat16) * (size_t)m->bpad * H));
-      if (int rc = make_tmap_bf16_2d(&t.map_h[pp], t.h[pp], (uint64_t)m->bpad, H,
-                                     kTileM, 64))
+      if (int rc = make_tmap_bf16_2d(&t.map_h[pp], t.h[pp], (uint64_t)m->bpad, H, kTileM, 64))
         return rc;
     }
   }
   if (int rc = tc_alloc(m, &m->w_fc, (size_t)C * H)) return rc;
-  to_bf16_kernel<<<blocks((size_t)C * H), TPB>>>(m->P(ix.w_fc()), m->w_fc,
-                                                 (size_t)C * H);
-  if (int rc = make_tmap_bf16_2d(&m->map_w_fc, m->w_fc, (uint64_t)C, H, C, 64))
-    return rc;
+  to_bf16_kernel<<<blocks((size_t)C * H), TPB>>>(m->P(ix.w_fc()), m->w_fc, (size_t)C * H);
+  if (int rc = make_tmap_bf16_2d(&m->map_w_fc, m->w_fc, (uint64_t)C, H, C, 64)) return rc;
   B200_CUDA(cudaGetLastError());
 
-  B200_CUDA(cudaFuncSetAttribute(gru_tc_kernel<MODE_L0>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 TcCfg<MODE_L0>::SMEM_BYTES));
-  B200_CUDA(cudaFuncSetAttribute(gru_tc_kernel<MODE_LN>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 TcCfg<MODE_LN>::SMEM_BYTES));
-  B200_CUDA(cudaFuncSetAttribute(gru_tc_kernel<MODE_FC>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 TcCfg<MODE_FC>::SMEM_BYTES));
+  B200_CUDA(cudaFuncSetAttribute(gru_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 L_SMEM_BYTES));
+  B200_CUDA(cudaFuncSetAttribute(fc_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 F_SMEM_BYTES));
   return 0;
 }
 
@@ -503,42 +630,36 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
   int launches = 0;
   const int m_tiles = (n + kTileM - 1) / kTileM;
   const int rows = m_tiles * kTileM;
-  tc_init_kernel<<<(rows + 255) / 256, 256, 0, s>>>(m->chars, m->alive, n, rows,
-                                                    c.sos);
-  ++launches;
+  {
+    size_t total = (size_t)rows * m->kx;
+    tc_init_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(
+        m->chars, m->alive, m->onehot, n, rows, m->kx, c.sos);
+    ++launches;
+  }
   for (int step = 0; step < T; ++step) {
     const int rd = step & 1, wr = rd ^ 1;  // ping-pong hidden buffers
     for (int l = 0; l < L; ++l) {
       TcLayer &t = m->tc[l];
-      TcArgs a{};
+      LayerArgs a{};
       a.n = n; a.m_tiles = m_tiles; a.n_blocks = H / kUnitBlock;
-      a.kb_x = (l == 0) ? 0 : H / TC_BLOCK_K;
+      a.kb_x = (l == 0 ? m->kx : H) / TC_BLOCK_K;
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
-      a.H = H; a.C = C; a.T = T; a.step = step; a.eos = c.eos;
-      a.t0 = m->t0_tc; a.bias = t.bias; a.chars = m->chars;
-      a.h_prev = t.h[rd]; a.h_out = t.h[wr];
+      a.H = H; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
       const int tiles = a.m_tiles * a.n_blocks;
       const int grid = tiles < sms ? tiles : sms;
-      if (l == 0) {
-        gru_tc_kernel<MODE_L0><<<grid, TC_THREADS, TcCfg<MODE_L0>::SMEM_BYTES, s>>>(
-            t.map_h[rd], t.map_h[rd], t.map_w_hh, t.map_w_hh, a);
-      } else {
-        gru_tc_kernel<MODE_LN><<<grid, TC_THREADS, TcCfg<MODE_LN>::SMEM_BYTES, s>>>(
-            m->tc[l - 1].map_h[wr], t.map_h[rd], t.map_w_ih, t.map_w_hh, a);
-      }
+      gru_layer_kernel<<<grid, L_THREADS, L_SMEM_BYTES, s>>>(
+          l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
+          l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, a);
       ++launches;
     }
-    TcArgs a{};
-    a.n = n; a.m_tiles = m_tiles; a.n_blocks = 1;
-    a.kb_x = H / TC_BLOCK_K; a.kb_h = 0;
-    a.H = H; a.C = C; a.T = T; a.step = step; a.eos = c.eos;
-    a.b_fc = m->b_fc; a.logits = m->logits;
+    FcArgs a{};
+    a.n = n; a.m_tiles = m_tiles; a.kb = H / TC_BLOCK_K; a.H = H; a.C = C; a.T = T;
+    a.step = step; a.eos = c.eos; a.kx = m->kx;
+    a.b_fc = m->b_fc; a.logits = m->debug_logits ? m->logits : nullptr;
     a.rfloats = io->rfloats; a.output = io->output;
-    a.chars_out = m->chars; a.alive = m->alive;
+    a.chars = m->chars; a.alive = m->alive; a.onehot = m->onehot;
     const int grid = m_tiles < sms ? m_tiles : sms;
-    const CUtensorMap &mx = m->tc[L - 1].map_h[wr];
-    gru_tc_kernel<MODE_FC><<<grid, TC_THREADS, TcCfg<MODE_FC>::SMEM_BYTES, s>>>(
-        mx, mx, m->map_w_fc, m->map_w_fc, a);
+    fc_sample_kernel<<<grid, F_THREADS, F_SMEM_BYTES, s>>>(m->tc[L - 1].map_h[wr], m->map_w_fc, a);
     ++launches;
   }
   if (io->done_flag) {
@@ -552,11 +673,10 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
 
 }  // namespace b200gru
 
-// Plain tcgen05 GEMM through the same pipeline (FC mode with the sampling
-// epilogue replaced by a store) — used by tests to validate the TMA / UMMA
-// descriptor plumbing in isolation.
+// Plain tcgen05 GEMM through the same TMA / UMMA / TMEM plumbing with a store
+// epilogue — used by tests to validate descriptors in isolation.
 namespace b200gru {
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(256, 1)
 gemm_probe_kernel(const __grid_constant__ CUtensorMap map_a,
                   const __grid_constant__ CUtensorMap map_b, float *d, int M,
                   int N, int K, int n_tile) {
@@ -654,7 +774,7 @@ extern "C" int b200gru_gemm_bf16_tn(const void *a, const void *b, float *d,
   B200_CUDA(cudaFuncSetAttribute(gemm_probe_kernel,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   dim3 grid(n / n_tile, (m + kTileM - 1) / kTileM);
-  gemm_probe_kernel<<<grid, TC_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
+  gemm_probe_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
       ma, mb, d, m, n, k, n_tile);
   B200_CUDA(cudaGetLastError());
   return 0;

@@ -20,9 +20,9 @@ constexpr int kUnitBlock = 64;  // hidden units per tile (x3 / x4 gate columns)
 constexpr int kExactChunk = 8192;
 
 struct TcLayer {
-  __nv_bfloat16 *w_ih = nullptr;  // packed [H/64][192][K]  (layers >= 1)
-  __nv_bfloat16 *w_hh = nullptr;  // packed [H/64][192][H]
-  float *bias = nullptr;          // [H/64][4][64]: b_r(+hr), b_z(+hz), b_in, b_hn
+  __nv_bfloat16 *w_ih = nullptr;  // packed [H/64][n|r|z x 64][H]  (layers >= 1)
+  __nv_bfloat16 *w_hh = nullptr;  // packed [H/64][r|z|n x 64][H]
+  float *bias = nullptr;          // [H/64][4][64]: b_in, b_r(+hr), b_z(+hz), b_hn
   CUtensorMap map_w_ih, map_w_hh;
   CUtensorMap map_h[2];           // A-operand maps over the two h buffers
   __nv_bfloat16 *h[2] = {nullptr, nullptr};  // [bpad, H] ping-pong
@@ -53,7 +53,11 @@ struct b200gru_model {
   int32_t *chars = nullptr; // [bpad]
   uint8_t *alive = nullptr; // [bpad]
   // --- tensor-core path
-  float *t0_tc = nullptr;   // [C, H/64, 3, 64], b_ih (+ b_hr, b_hz) folded
+  int kx = 0;                        // one-hot row length: num_char rounded up to 64
+  __nv_bfloat16 *onehot = nullptr;   // [bpad, kx]  layer-0 x operand
+  __nv_bfloat16 *t0w = nullptr;      // [H/64][192][kx] layer-0 table as K-major weights
+  CUtensorMap map_onehot, map_t0w;
+  bool debug_logits = false;         // FC kernel also stores pre-softmax logits
   b200gru::TcLayer tc[B200GRU_MAX_LAYERS];
   __nv_bfloat16 *w_fc = nullptr;  // [C, H] bf16
   CUtensorMap map_w_fc;

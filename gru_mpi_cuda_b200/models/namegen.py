@@ -106,6 +106,10 @@ class NameGenerator:
             torch.cuda.current_stream().synchronize()
         return host.clone()
 
+    def enable_logits_tap(self, on: bool = True) -> None:
+        """Make the tensor-core FC kernel store its logits too (slow; tests only)."""
+        _native.check(self._lib.b200gru_model_set_debug(self._h, 1 if on else 0))
+
     def debug_logits(self, n: int) -> torch.Tensor:
         """Last step's pre-softmax FC outputs for the first `n` names."""
         out = torch.empty(n, self.cfg.num_char, dtype=torch.float32, device=torch.device("cuda", self.device))

@@ -137,7 +137,10 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
                      void *stream);
 /* Number of kernel launches the last b200gru_generate() issued. */
 int b200gru_last_launch_count(const b200gru_model *m);
-/* Debug taps: copy the model's last-step logits [n, num_char] (fp32). */
+/* Debug taps.  set_debug(m, 1) makes the tensor-core FC kernel also store its
+ * pre-softmax logits (costly: off by default); debug_logits copies the last
+ * step's logits [n, num_char] (fp32).  The exact path always keeps them. */
+int b200gru_model_set_debug(b200gru_model *m, int logits_tap);
 int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
                          void *stream);
 

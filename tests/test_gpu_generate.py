@@ -77,8 +77,10 @@ def test_tc_logits_against_fp32_reference(gen_tiny, tiny_cfg, tiny_params):
     tensor-core path actually sampled and compare final-step logits."""
     n = 256
     r = W.random_floats(n * tiny_cfg.max_len, 24)
+    gen_tiny.enable_logits_tap(True)
     got = gen_tiny.generate(n, r, mode="tc")
     logits = gen_tiny.debug_logits(n).cpu()
+    gen_tiny.enable_logits_tap(False)
     model = TorchNameGen.from_flat(tiny_cfg, tiny_params)
     chars = torch.full((n,), tiny_cfg.sos, dtype=torch.long)
     h = torch.zeros(tiny_cfg.num_layers, n, tiny_cfg.hidden)
