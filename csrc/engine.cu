@@ -108,7 +108,7 @@ int b200gru_model_create(const b200gru_config *cfg, const float *params,
   m->cfg = *cfg;
   m->device = device;
   m->max_batch = max_batch;
-  m->bpad = (max_batch + kTileM - 1) / kTileM * kTileM;
+  m->bpad = (max_batch + 2 * kTileM - 1) / (2 * kTileM) * (2 * kTileM);  // whole CTA-pair tiles
   m->lay = build_layout(*cfg);
   int rc = create_impl(m, params);
   if (rc) {

@@ -37,6 +37,8 @@
 //   warp 4..  epilogue       tcgen05.ld -> gate math in registers -> global
 // The accumulator is double-buffered in TMEM so the epilogue of tile i
 // overlaps the MMAs of tile i+1.
+#include <cstdlib>
+
 #include "model.hpp"
 #include "sm100_ptx.cuh"
 
@@ -67,6 +69,66 @@ struct LayerArgs {
   const __nv_bfloat16 *h_prev;  // [bpad, H]
   __nv_bfloat16 *h_out;         // [bpad, H]
 };
+
+// Gate math for one thread's (name, 32 units) slice of a finished tile:
+// t addresses this warp's TMEM lanes at the slice's first n_i column.
+__device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
+                                              const float4 *bias4,
+                                              __nv_bfloat16 *h_out, bool valid) {
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch) {
+    uint32_t vn[16], vr[16], vz[16], vh[16];
+    tmem_ld16(t + ch * 16, vn);
+    tmem_ld16(t + 64 + ch * 16, vr);
+    tmem_ld16(t + 128 + ch * 16, vz);
+    tmem_ld16(t + 192 + ch * 16, vh);
+    tmem_ld_wait();
+    const uint32_t hw[8] = {hq[2 * ch].x,     hq[2 * ch].y,     hq[2 * ch].z,
+                            hq[2 * ch].w,     hq[2 * ch + 1].x, hq[2 * ch + 1].y,
+                            hq[2 * ch + 1].z, hq[2 * ch + 1].w};
+    uint32_t packed[8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {  // 4 units per float4 of bias
+      const float4 b_in = __ldg(bias4 + ch * 4 + q);
+      const float4 b_r = __ldg(bias4 + 16 + ch * 4 + q);
+      const float4 b_z = __ldg(bias4 + 32 + ch * 4 + q);
+      const float4 b_hn = __ldg(bias4 + 48 + ch * 4 + q);
+      const float bi[4] = {b_in.x, b_in.y, b_in.z, b_in.w};
+      const float br[4] = {b_r.x, b_r.y, b_r.z, b_r.w};
+      const float bz[4] = {b_z.x, b_z.y, b_z.z, b_z.w};
+      const float bh[4] = {b_hn.x, b_hn.y, b_hn.z, b_hn.w};
+      float hn[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = q * 4 + e;
+        const uint32_t w = hw[i >> 1];
+        const float hp = __uint_as_float((i & 1) ? (w & 0xFFFF0000u) : (w << 16));
+        const float r = sigmoid_approx(__uint_as_float(vr[i]) + br[e]);
+        const float z = sigmoid_approx(__uint_as_float(vz[i]) + bz[e]);
+        const float nn = tanh_approx(fmaf(r, __uint_as_float(vh[i]) + bh[e],
+                                          __uint_as_float(vn[i]) + bi[e]));
+        // h' = (1-z)*n + z*h  ==  n + z*(h - n)     (ref:752-763)
+        hn[e] = fmaf(z, hp - nn, nn);
+      }
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(hn[0], hn[1]);
+      __nv_bfloat162 p1 = __floats2bfloat162_rn(hn[2], hn[3]);
+      packed[q * 2] = *reinterpret_cast<uint32_t *>(&p0);
+      packed[q * 2 + 1] = *reinterpret_cast<uint32_t *>(&p1);
+    }
+    if (valid) {
+      uint4 *dst = reinterpret_cast<uint4 *>(h_out + ch * 16);
+      dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    }
+  }
+  // re-zero this warp's n_h columns before the stage goes back to the MMAs
+  uint32_t zero[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) zero[i] = 0u;
+  tmem_st16(t + 192, zero);
+  tmem_st16(t + 192 + 16, zero);
+  tmem_st_wait();
+}
 
 __global__ void __launch_bounds__(L_THREADS, 1)
 gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
@@ -133,60 +195,64 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
 
   if (warp == 0) {
     // ===================================================== TMA producer
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m_tile = tile / args.n_blocks;
-        const int n_blk = tile % args.n_blocks;
-        for (int kb = 0; kb < kb_total; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+    // The whole warp walks the loop (so everything stays warp-uniform and
+    // ptxas keeps descriptors in uniform registers); one elected lane issues.
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int m_tile = tile / args.n_blocks;
+      const int n_blk = tile % args.n_blocks;
+      for (int kb = 0; kb < kb_total; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
           uint8_t *sa = smem + stage * L_STAGE_BYTES;
           uint8_t *sb = sa + TC_A_BYTES;
           mbar_expect_tx(&full_bar[stage], TC_A_BYTES + L_B_BYTES);
           const bool is_x = kb < args.kb_x;
           const int k = (is_x ? kb : kb - args.kb_x) * TC_BLOCK_K;
-          tma_load_2d(sa, is_x ? &map_x : &map_h, &full_bar[stage], k,
-                      m_tile * kTileM);
-          tma_load_2d(sb, is_x ? &map_wx : &map_wh, &full_bar[stage], k,
-                      n_blk * 192);
-          if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
+          tma_load_2d(sa, is_x ? &map_x : &map_h, &full_bar[stage], k, m_tile * kTileM);
+          tma_load_2d(sb, is_x ? &map_wx : &map_wh, &full_bar[stage], k, n_blk * 192);
         }
+        __syncwarp();
+        if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ======================================================= MMA issuer
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc_stage = 0;
-      uint32_t acc_phase = 0;
-      const uint32_t idesc = umma_idesc_bf16(kTileM, 192);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc_stage = 0;
+    uint32_t acc_phase = 0;
+    const uint32_t idesc = umma_idesc_bf16(kTileM, 192);
+    const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
+      for (int kb = 0; kb < kb_total; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
-        for (int kb = 0; kb < kb_total; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * L_STAGE_BYTES);
-          const uint64_t da = umma_desc_sw128(sa);
-          const uint64_t db = umma_desc_sw128(sa + TC_A_BYTES);
-          const bool is_x = kb < args.kb_x;
-#pragma unroll
-          for (int k = 0; k < TC_BLOCK_K / 16; ++k) {
-            const uint64_t koff = (uint64_t)(k * 32 >> 4);  // 32 B per UMMA_K
-            if (is_x)  // [n_i | r | z]: the tile's first MMA overwrites
-              umma_bf16(d, da + koff, db + koff, idesc, (kb | k) != 0 ? 1u : 0u);
-            else       // [r | z | n_h]: always accumulates (n_h pre-zeroed)
-              umma_bf16(d + 64, da + koff, db + koff, idesc, 1u);
+        if (elect_one()) {
+          const uint64_t da = desc0 + (uint64_t)((stage * L_STAGE_BYTES) >> 4);
+          const uint64_t db = da + (uint64_t)(TC_A_BYTES >> 4);
+          if (kb < args.kb_x) {  // [n_i | r | z]: the tile's first MMA overwrites
+            umma_bf16(d, da, db, idesc, kb != 0 ? 1u : 0u);
+            umma_bf16(d, da + 2, db + 2, idesc, 1u);
+            umma_bf16(d, da + 4, db + 4, idesc, 1u);
+            umma_bf16(d, da + 6, db + 6, idesc, 1u);
+          } else {               // [r | z | n_h]: accumulates (n_h pre-zeroed)
+            umma_bf16(d + 64, da, db, idesc, 1u);
+            umma_bf16(d + 64, da + 2, db + 2, idesc, 1u);
+            umma_bf16(d + 64, da + 4, db + 4, idesc, 1u);
+            umma_bf16(d + 64, da + 6, db + 6, idesc, 1u);
           }
           umma_commit(&empty_bar[stage]);  // smem slot free when MMAs retire
-          if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
+          if (kb == kb_total - 1) umma_commit(&tmem_full[acc_stage]);  // accumulator ready
         }
-        umma_commit(&tmem_full[acc_stage]);  // accumulator ready
-        if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+        __syncwarp();
+        if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
       }
+      if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
   } else if (warp >= 4) {
     // ========================================================= epilogue
@@ -221,61 +287,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
-#pragma unroll
-      for (int ch = 0; ch < 2; ++ch) {
-        uint32_t vn[16], vr[16], vz[16], vh[16];
-        tmem_ld16(t + ch * 16, vn);
-        tmem_ld16(t + 64 + ch * 16, vr);
-        tmem_ld16(t + 128 + ch * 16, vz);
-        tmem_ld16(t + 192 + ch * 16, vh);
-        tmem_ld_wait();
-        const uint32_t hw[8] = {hq[2 * ch].x,     hq[2 * ch].y,     hq[2 * ch].z,
-                                hq[2 * ch].w,     hq[2 * ch + 1].x, hq[2 * ch + 1].y,
-                                hq[2 * ch + 1].z, hq[2 * ch + 1].w};
-        uint32_t packed[8];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {  // 4 units per float4 of bias
-          const float4 b_in = __ldg(bias4 + ch * 4 + q);
-          const float4 b_r = __ldg(bias4 + 16 + ch * 4 + q);
-          const float4 b_z = __ldg(bias4 + 32 + ch * 4 + q);
-          const float4 b_hn = __ldg(bias4 + 48 + ch * 4 + q);
-          const float bi[4] = {b_in.x, b_in.y, b_in.z, b_in.w};
-          const float br[4] = {b_r.x, b_r.y, b_r.z, b_r.w};
-          const float bz[4] = {b_z.x, b_z.y, b_z.z, b_z.w};
-          const float bh[4] = {b_hn.x, b_hn.y, b_hn.z, b_hn.w};
-          float hn[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int i = q * 4 + e;
-            const uint32_t w = hw[i >> 1];
-            const float hp = __uint_as_float((i & 1) ? (w & 0xFFFF0000u) : (w << 16));
-            const float r = sigmoid_approx(__uint_as_float(vr[i]) + br[e]);
-            const float z = sigmoid_approx(__uint_as_float(vz[i]) + bz[e]);
-            const float nn = tanh_approx(fmaf(r, __uint_as_float(vh[i]) + bh[e],
-                                              __uint_as_float(vn[i]) + bi[e]));
-            // h' = (1-z)*n + z*h  ==  n + z*(h - n)     (ref:752-763)
-            hn[e] = fmaf(z, hp - nn, nn);
-          }
-          __nv_bfloat162 p0 = __floats2bfloat162_rn(hn[0], hn[1]);
-          __nv_bfloat162 p1 = __floats2bfloat162_rn(hn[2], hn[3]);
-          packed[q * 2] = *reinterpret_cast<uint32_t *>(&p0);
-          packed[q * 2 + 1] = *reinterpret_cast<uint32_t *>(&p1);
-        }
-        if (valid) {
-          uint4 *dst = reinterpret_cast<uint4 *>(args.h_out + hoff + ch * 16);
-          dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-          dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
-        }
-      }
-      // re-zero this warp's n_h columns, then hand the stage back
-      {
-        uint32_t zero[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) zero[i] = 0u;
-        tmem_st16(t + 192, zero);
-        tmem_st16(t + 192 + 16, zero);
-        tmem_st_wait();
-      }
+      gate_epilogue(t, hq, bias4, args.h_out + hoff, valid);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
@@ -288,6 +300,194 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<TC_TMEM_COLS>(tmem_base);
+  }
+}
+
+// ------------------------------------------------- layers, CTA pairs (2-SM MMA)
+// Same math, but two CTAs of one cluster (one TPC) work on a 256-name tile with
+// tcgen05.mma.cta_group::2: each CTA stages its own 128 rows of A and only HALF
+// of the weight block (96 of the 192 rows), the tensor cores of both SMs read
+// both halves.  Shared-memory traffic per MMA flop drops by 30%, which is what
+// bounds the single-CTA kernel (TMA fill + UMMA operand reads share 128 B/clk).
+//   leader (cluster rank 0): issues every MMA; its `full` barrier collects the
+//     TMA bytes of BOTH CTAs; its tmem_empty barrier collects the epilogue
+//     arrivals of BOTH CTAs.
+//   tcgen05.commit multicasts to the `empty` / tmem_full barriers of both CTAs.
+constexpr int P_B_BYTES = 96 * 128;          // 12 KB: this CTA's half of B
+constexpr int P_STAGE_BYTES = TC_A_BYTES + P_B_BYTES;
+constexpr int P_STAGES = 7;
+constexpr int P_SMEM_BYTES = P_STAGES * P_STAGE_BYTES + 1024 + 256;
+
+__global__ void __launch_bounds__(L_THREADS, 1)
+gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
+                      const __grid_constant__ CUtensorMap map_h,
+                      const __grid_constant__ CUtensorMap map_wx,
+                      const __grid_constant__ CUtensorMap map_wh,
+                      const LayerArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + P_STAGES * P_STAGE_BYTES);
+  uint64_t *full_bar = bars;                       // [STAGES] (leader's is used)
+  uint64_t *empty_bar = bars + P_STAGES;           // [STAGES] (each CTA its own)
+  uint64_t *tmem_full = bars + 2 * P_STAGES;       // [2]      (each CTA its own)
+  uint64_t *tmem_empty = bars + 2 * P_STAGES + 2;  // [2]      (leader's is used)
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * P_STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const int m2_tiles = (args.m_tiles + 1) >> 1;    // 256-name tiles
+  const int total_tiles = m2_tiles * args.n_blocks;
+  const int kb_total = args.kb_x + args.kb_h;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_x);
+    tma_prefetch_desc(&map_wx);
+    if (args.kb_h) { tma_prefetch_desc(&map_h); tma_prefetch_desc(&map_wh); }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < P_STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 2 * L_EPI_WARPS);  // epilogue warps of both CTAs
+    }
+    fence_mbar_init();
+  }
+  cluster_sync_all();  // barrier inits visible pair-wide before any remote use
+  if (warp == 2) tmem_alloc_2sm<TC_TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp >= 4) {  // n_h columns of both stages start at zero
+    const uint32_t lane_base0 = (uint32_t)((warp & 3) * 32) << 16;
+    const int half0 = (warp - 4) >> 2;
+    uint32_t zero[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) zero[i] = 0u;
+#pragma unroll
+    for (int st = 0; st < 2; ++st)
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+        tmem_st16(tmem_base + lane_base0 + st * TC_ACC_STRIDE + 192 + half0 * 32 + c * 16, zero);
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // both CTAs allocated + zeroed before the leader's MMAs
+  tc_fence_after();
+
+  if (warp == 0) {
+    // ============================ TMA producer (both CTAs, own smem)
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+      const int m2 = tile / args.n_blocks;
+      const int n_blk = tile % args.n_blocks;
+      for (int kb = 0; kb < kb_total; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
+          uint8_t *sa = smem + stage * P_STAGE_BYTES;
+          uint8_t *sb = sa + TC_A_BYTES;
+          // bytes of both CTAs land on the leader's barrier
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * P_STAGE_BYTES);
+          const uint32_t bar = mapa_u32(&full_bar[stage], 0);
+          const bool is_x = kb < args.kb_x;
+          const int k = (is_x ? kb : kb - args.kb_x) * TC_BLOCK_K;
+          tma_load_2d_2sm(sa, is_x ? &map_x : &map_h, bar, k, (m2 * 2 + (int)rank) * kTileM);
+          tma_load_2d_2sm(sb, is_x ? &map_wx : &map_wh, bar, k, n_blk * 192 + (int)rank * 96);
+        }
+        __syncwarp();
+        if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ========================================== MMA issuer (leader only)
+    if (leader) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc_stage = 0;
+      uint32_t acc_phase = 0;
+      const uint32_t idesc = umma_idesc_bf16(2 * kTileM, 192);
+      const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
+        for (int kb = 0; kb < kb_total; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint64_t da = desc0 + (uint64_t)((stage * P_STAGE_BYTES) >> 4);
+            const uint64_t db = da + (uint64_t)(TC_A_BYTES >> 4);
+            if (kb < args.kb_x) {
+              umma_bf16_2sm(d, da, db, idesc, kb != 0 ? 1u : 0u);
+              umma_bf16_2sm(d, da + 2, db + 2, idesc, 1u);
+              umma_bf16_2sm(d, da + 4, db + 4, idesc, 1u);
+              umma_bf16_2sm(d, da + 6, db + 6, idesc, 1u);
+            } else {
+              umma_bf16_2sm(d + 64, da, db, idesc, 1u);
+              umma_bf16_2sm(d + 64, da + 2, db + 2, idesc, 1u);
+              umma_bf16_2sm(d + 64, da + 4, db + 4, idesc, 1u);
+              umma_bf16_2sm(d + 64, da + 6, db + 6, idesc, 1u);
+            }
+            umma_commit_2sm(&empty_bar[stage], 0b11);  // frees the slot in both CTAs
+            if (kb == kb_total - 1) umma_commit_2sm(&tmem_full[acc_stage], 0b11);  // wakes both epilogues
+          }
+          __syncwarp();
+          if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
+        }
+        if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ======================================== epilogue (both CTAs, own rows)
+    const int quarter = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+    int acc_stage = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+      const int m2 = tile / args.n_blocks;
+      const int n_blk = tile % args.n_blocks;
+      const int row = (m2 * 2 + (int)rank) * kTileM + quarter * 32 + lane;
+      const bool valid = row < args.n;
+      const bool has_h = args.kb_h > 0;
+      const size_t hoff = (size_t)row * args.H + (size_t)n_blk * 64 + half * 32;
+      uint4 hq[4];
+      if (has_h && valid) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(args.h_prev + hoff);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hq[i] = src[i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hq[i] = make_uint4(0, 0, 0, 0);
+      }
+      const float4 *bias4 =
+          reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
+      mbar_wait(&tmem_full[acc_stage], acc_phase);
+      tc_fence_after();
+      const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
+      gate_epilogue(t, hq, bias4, args.h_out + hoff, valid);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
+      if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // peer smem / barriers stay valid until both are done
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2sm<TC_TMEM_COLS>(tmem_base);
   }
 }
 
@@ -607,8 +807,22 @@ int tc_prepare(b200gru_model *m) {
   if (int rc = make_tmap_bf16_2d(&m->map_w_fc, m->w_fc, (uint64_t)C, H, C, 64)) return rc;
   B200_CUDA(cudaGetLastError());
 
+  // CTA-pair variants of the weight maps: each CTA of a pair loads 96 rows
+  if (int rc = make_tmap_bf16_2d(&m->map_t0w_p, m->t0w, 3 * (uint64_t)H, kx, 96, 64)) return rc;
+  for (int l = 0; l < L; ++l) {
+    TcLayer &t = m->tc[l];
+    if (l > 0)
+      if (int rc = make_tmap_bf16_2d(&t.map_w_ih_p, t.w_ih, 3 * (uint64_t)H, H, 96, 64)) return rc;
+    if (int rc = make_tmap_bf16_2d(&t.map_w_hh_p, t.w_hh, 3 * (uint64_t)H, H, 96, 64)) return rc;
+  }
   B200_CUDA(cudaFuncSetAttribute(gru_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  L_SMEM_BYTES));
+  B200_CUDA(cudaFuncSetAttribute(gru_layer_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 P_SMEM_BYTES));
+  {
+    const char *e = getenv("B200GRU_CTA_PAIRS");
+    m->use_pairs = !(e && e[0] == '0');
+  }
   B200_CUDA(cudaFuncSetAttribute(fc_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  F_SMEM_BYTES));
   return 0;
@@ -646,10 +860,31 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
       a.H = H; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
       const int tiles = a.m_tiles * a.n_blocks;
-      const int grid = tiles < sms ? tiles : sms;
-      gru_layer_kernel<<<grid, L_THREADS, L_SMEM_BYTES, s>>>(
-          l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-          l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, a);
+      if (m->use_pairs && m_tiles >= 2) {
+        // 256-name tiles on CTA pairs (clusters of 2, one pair per TPC)
+        const int tiles2 = ((m_tiles + 1) / 2) * a.n_blocks;
+        const int pairs = tiles2 < sms / 2 ? tiles2 : sms / 2;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(2 * pairs);
+        cfg.blockDim = dim3(L_THREADS);
+        cfg.dynamicSmemBytes = P_SMEM_BYTES;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_pair_kernel,
+                                     l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
+                                     l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p, a));
+      } else {
+        const int grid = tiles < sms ? tiles : sms;
+        gru_layer_kernel<<<grid, L_THREADS, L_SMEM_BYTES, s>>>(
+            l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
+            l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, a);
+      }
       ++launches;
     }
     FcArgs a{};

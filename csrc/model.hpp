@@ -24,6 +24,7 @@ struct TcLayer {
   __nv_bfloat16 *w_hh = nullptr;  // packed [H/64][r|z|n x 64][H]
   float *bias = nullptr;          // [H/64][4][64]: b_in, b_r(+hr), b_z(+hz), b_hn
   CUtensorMap map_w_ih, map_w_hh;
+  CUtensorMap map_w_ih_p, map_w_hh_p;  // 96-row boxes for the CTA-pair kernel
   CUtensorMap map_h[2];           // A-operand maps over the two h buffers
   __nv_bfloat16 *h[2] = {nullptr, nullptr};  // [bpad, H] ping-pong
 };
@@ -56,7 +57,8 @@ struct b200gru_model {
   int kx = 0;                        // one-hot row length: num_char rounded up to 64
   __nv_bfloat16 *onehot = nullptr;   // [bpad, kx]  layer-0 x operand
   __nv_bfloat16 *t0w = nullptr;      // [H/64][192][kx] layer-0 table as K-major weights
-  CUtensorMap map_onehot, map_t0w;
+  CUtensorMap map_onehot, map_t0w, map_t0w_p;
+  bool use_pairs = true;             // cta_group::2 layer kernel (B200GRU_CTA_PAIRS=0 disables)
   bool debug_logits = false;         // FC kernel also stores pre-softmax logits
   b200gru::TcLayer tc[B200GRU_MAX_LAYERS];
   __nv_bfloat16 *w_fc = nullptr;  // [C, H] bf16
