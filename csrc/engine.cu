@@ -67,9 +67,11 @@ int create_impl(b200gru_model *m, const float *params_host) {
   // C9: activation buffers, sized once.
   m->chunk = m->max_batch < kExactChunk ? m->max_batch : kExactChunk;
   if (int rc = dev_alloc(m, &m->t0_raw, (size_t)C * 3 * H)) return rc;
-  if (int rc = dev_alloc(m, &m->g_ih, (size_t)m->chunk * 3 * H)) return rc;
-  if (int rc = dev_alloc(m, &m->g_hh, (size_t)m->chunk * 3 * H)) return rc;
-  if (int rc = dev_alloc(m, &m->h32, (size_t)L * m->chunk * H)) return rc;
+  if (m->tp_world == 1) {  // the fp32 exact path is single-rank-per-model only
+    if (int rc = dev_alloc(m, &m->g_ih, (size_t)m->chunk * 3 * H)) return rc;
+    if (int rc = dev_alloc(m, &m->g_hh, (size_t)m->chunk * 3 * H)) return rc;
+    if (int rc = dev_alloc(m, &m->h32, (size_t)L * m->chunk * H)) return rc;
+  }
   if (int rc = dev_alloc(m, &m->logits, (size_t)m->bpad * C)) return rc;
   if (int rc = dev_alloc(m, &m->chars, (size_t)m->bpad)) return rc;
   if (int rc = dev_alloc(m, &m->alive, (size_t)m->bpad)) return rc;
@@ -84,7 +86,10 @@ int create_impl(b200gru_model *m, const float *params_host) {
     return rc;
 
   // Tensor-core path needs 64-aligned hidden size and a single-UMMA FC.
-  m->tc_ok = (H % kUnitBlock == 0) && (C % 16 == 0) && C >= 16 && C <= 256;
+  m->tc_ok = (H % (kUnitBlock * m->tp_world) == 0) && (C % 16 == 0) && C >= 16 && C <= 256;
+  if (m->tp_world > 1 && !m->tc_ok)
+    return fail(B200GRU_ERR_ARG, "tensor parallel needs hidden %% (64*world) == 0 and num_char a "
+                                 "multiple of 16 in [16,256] (H=%d, world=%d, C=%d)", H, m->tp_world, C);
   if (m->tc_ok)
     if (int rc = tc_prepare(m)) return rc;
   B200_CUDA(cudaDeviceSynchronize());
@@ -97,9 +102,27 @@ extern "C" {
 
 int b200gru_model_create(const b200gru_config *cfg, const float *params,
                          int device, int max_batch, b200gru_model **out) {
+  return b200gru_model_create_tp(cfg, params, device, max_batch, 0, 1, out);
+}
+
+size_t b200gru_tp_shared_bytes(const b200gru_model *m) {
+  return (m && m->tp_world > 1) ? tp_shared_bytes(m) : 0;
+}
+
+int b200gru_tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
+  B200_REQUIRE(m && local_base && peer_bases, "null argument");
+  DeviceGuard guard(m->device);
+  return tp_bind(m, local_base, peer_bases);
+}
+
+int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
+                            int device, int max_batch, int tp_rank, int tp_world,
+                            b200gru_model **out) {
   if (int rc = validate_config(cfg)) return rc;
   B200_REQUIRE(params && out, "null argument");
   B200_REQUIRE(max_batch > 0, "max_batch must be positive");
+  B200_REQUIRE(tp_world >= 1 && tp_world <= 8 && tp_rank >= 0 && tp_rank < tp_world,
+               "tensor-parallel rank %d of %d", tp_rank, tp_world);
   int ndev = 0;
   B200_CUDA(cudaGetDeviceCount(&ndev));
   B200_REQUIRE(device >= 0 && device < ndev, "device %d of %d", device, ndev);
@@ -108,6 +131,8 @@ int b200gru_model_create(const b200gru_config *cfg, const float *params,
   m->cfg = *cfg;
   m->device = device;
   m->max_batch = max_batch;
+  m->tp_rank = tp_rank;
+  m->tp_world = tp_world;
   m->bpad = (max_batch + 2 * kTileM - 1) / (2 * kTileM) * (2 * kTileM);  // whole CTA-pair tiles
   m->lay = build_layout(*cfg);
   int rc = create_impl(m, params);
@@ -148,7 +173,11 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   m->last_launches = 0;
   if (n == 0 && !io->done_flag) return 0;
-  if (mode == B200GRU_MODE_EXACT) return exact_generate(m, n, io, s);
+  if (mode == B200GRU_MODE_EXACT) {
+    if (m->tp_world > 1)
+      return fail(B200GRU_ERR_ARG, "the fp32 exact path does not run tensor parallel");
+    return exact_generate(m, n, io, s);
+  }
   if (mode == B200GRU_MODE_TC) {
     if (!m->tc_ok)
       return fail(B200GRU_ERR_ARG,

@@ -68,13 +68,43 @@ struct LayerArgs {
   const float *bias;            // [H/64, 4, 64]: b_in, b_r, b_z, b_hn
   const __nv_bfloat16 *h_prev;  // [bpad, H]
   __nv_bfloat16 *h_out;         // [bpad, H]
+  // ---- tensor parallel over the hidden dimension (tp_world == 1: off).
+  // This rank owns hidden columns [col0, col0 + 64*n_blocks).  Operand buffers
+  // are full width on every rank; each rank's epilogue stores its slice into
+  // every rank's copy (NVLink P2P) and bumps a per-(source rank, m-tile)
+  // counter there; the TMA producer of the consuming kernel waits on the
+  // counter of a source rank right before it loads that rank's K-chunk.
+  int tp_world, tp_rank;
+  int kb_rank;        // k-blocks per source rank in a full-width operand
+  int x_full;         // x operand is a full-width hidden buffer (layers >= 1)
+  int col0;
+  int flag_stride;    // counters per source rank
+  uint32_t expect_x, expect_h;
+  const uint32_t *wait_x, *wait_h;  // local counters [src][m_tile]
+  __nv_bfloat16 *h_out_peer[8];     // h_out on every rank ([tp_rank] == h_out)
+  uint32_t *signal_peer[8];         // this rank's counter row [m_tile] on every rank
 };
+
+// K-block order under tensor parallelism: start with the chunk this rank
+// produced itself, then walk the ring, so remote chunks have time to land.
+__device__ __forceinline__ int tp_kblock(int j, int kb_rank, int world, int rank, int *src) {
+  const int c = j / kb_rank;
+  int q = rank + c;
+  if (q >= world) q -= world;
+  *src = q;
+  return q * kb_rank + (j - c * kb_rank);
+}
+// All lanes poll (one coalesced request); every lane has then acquired.
+__device__ __forceinline__ void tp_wait_counter(const uint32_t *p, uint32_t expect) {
+  while ((int32_t)(ld_acquire_sys(p) - expect) < 0) __nanosleep(64);
+}
 
 // Gate math for one thread's (name, 32 units) slice of a finished tile:
 // t addresses this warp's TMEM lanes at the slice's first n_i column.
 __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
                                               const float4 *bias4,
-                                              __nv_bfloat16 *h_out, bool valid) {
+                                              __nv_bfloat16 *const *dsts, int ndst,
+                                              size_t hoff, bool valid) {
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     uint32_t vn[16], vr[16], vz[16], vh[16];
@@ -116,9 +146,13 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
       packed[q * 2 + 1] = *reinterpret_cast<uint32_t *>(&p1);
     }
     if (valid) {
-      uint4 *dst = reinterpret_cast<uint4 *>(h_out + ch * 16);
-      dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-      dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+      const uint4 lo = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      const uint4 hi = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+      for (int p = 0; p < ndst; ++p) {  // ndst > 1: the all-gather, as P2P stores
+        uint4 *dst = reinterpret_cast<uint4 *>(dsts[p] + hoff + ch * 16);
+        dst[0] = lo;
+        dst[1] = hi;
+      }
     }
   }
   // re-zero this warp's n_h columns before the stage goes back to the MMAs
@@ -203,15 +237,30 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       const int m_tile = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
       for (int kb = 0; kb < kb_total; ++kb) {
+        const bool is_x = kb < args.kb_x;
+        const int j = is_x ? kb : kb - args.kb_x;
+        int kblk = j;
+        bool tp_fence = false;
+        if (args.tp_world > 1 && (!is_x || args.x_full)) {
+          int src;
+          kblk = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
+          if (src != args.tp_rank) {
+            tp_fence = true;
+            if (j % args.kb_rank == 0)
+              tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
+                              is_x ? args.expect_x : args.expect_h);
+          }
+        }
         mbar_wait(&empty_bar[stage], phase ^ 1);
         if (elect_one()) {
           uint8_t *sa = smem + stage * L_STAGE_BYTES;
           uint8_t *sb = sa + TC_A_BYTES;
           mbar_expect_tx(&full_bar[stage], TC_A_BYTES + L_B_BYTES);
-          const bool is_x = kb < args.kb_x;
-          const int k = (is_x ? kb : kb - args.kb_x) * TC_BLOCK_K;
-          tma_load_2d(sa, is_x ? &map_x : &map_h, &full_bar[stage], k, m_tile * kTileM);
-          tma_load_2d(sb, is_x ? &map_wx : &map_wh, &full_bar[stage], k, n_blk * 192);
+          if (tp_fence) fence_proxy_async();  // remote generic-proxy writes -> TMA reads
+          tma_load_2d(sa, is_x ? &map_x : &map_h, &full_bar[stage], kblk * TC_BLOCK_K,
+                      m_tile * kTileM);
+          tma_load_2d(sb, is_x ? &map_wx : &map_wh, &full_bar[stage], kblk * TC_BLOCK_K,
+                      n_blk * 192);
         }
         __syncwarp();
         if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
@@ -269,7 +318,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       const int row = m_tile * kTileM + quarter * 32 + lane;
       const bool valid = row < args.n;
       const bool has_h = args.kb_h > 0;
-      const size_t hoff = (size_t)row * args.H + (size_t)n_blk * 64 + half * 32;
+      const size_t hoff = (size_t)row * args.H + args.col0 + (size_t)n_blk * 64 + half * 32;
       // previous hidden for this thread's 32 units: issue the loads before
       // waiting on the accumulator so their latency hides behind the MMAs
       uint4 hq[4];
@@ -287,10 +336,15 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
-      gate_epilogue(t, hq, bias4, args.h_out + hoff, valid);
+      gate_epilogue(t, hq, bias4, args.h_out_peer, args.tp_world, hoff, valid);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
+      if (args.tp_world > 1) {  // publish this warp's slice of (m_tile, n_blk)
+        __threadfence_system();
+        __syncwarp();
+        if (lane < args.tp_world) red_release_sys_add(args.signal_peer[lane] + m_tile, 1u);
+      }
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
   }
@@ -391,7 +445,22 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       const int m2 = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
+      const int m_tile = m2 * 2 + (int)rank;
       for (int kb = 0; kb < kb_total; ++kb) {
+        const bool is_x = kb < args.kb_x;
+        const int j = is_x ? kb : kb - args.kb_x;
+        int kblk = j;
+        bool tp_fence = false;
+        if (args.tp_world > 1 && (!is_x || args.x_full)) {
+          int src;
+          kblk = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
+          if (src != args.tp_rank) {
+            tp_fence = true;
+            if (j % args.kb_rank == 0)
+              tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
+                              is_x ? args.expect_x : args.expect_h);
+          }
+        }
         mbar_wait(&empty_bar[stage], phase ^ 1);
         if (elect_one()) {
           uint8_t *sa = smem + stage * P_STAGE_BYTES;
@@ -399,10 +468,10 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
           // bytes of both CTAs land on the leader's barrier
           if (leader) mbar_expect_tx(&full_bar[stage], 2 * P_STAGE_BYTES);
           const uint32_t bar = mapa_u32(&full_bar[stage], 0);
-          const bool is_x = kb < args.kb_x;
-          const int k = (is_x ? kb : kb - args.kb_x) * TC_BLOCK_K;
-          tma_load_2d_2sm(sa, is_x ? &map_x : &map_h, bar, k, (m2 * 2 + (int)rank) * kTileM);
-          tma_load_2d_2sm(sb, is_x ? &map_wx : &map_wh, bar, k, n_blk * 192 + (int)rank * 96);
+          if (tp_fence) fence_proxy_async();
+          tma_load_2d_2sm(sa, is_x ? &map_x : &map_h, bar, kblk * TC_BLOCK_K, m_tile * kTileM);
+          tma_load_2d_2sm(sb, is_x ? &map_wx : &map_wh, bar, kblk * TC_BLOCK_K,
+                          n_blk * 192 + (int)rank * 96);
         }
         __syncwarp();
         if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
@@ -457,10 +526,11 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       const int m2 = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
-      const int row = (m2 * 2 + (int)rank) * kTileM + quarter * 32 + lane;
+      const int m_tile = m2 * 2 + (int)rank;
+      const int row = m_tile * kTileM + quarter * 32 + lane;
       const bool valid = row < args.n;
       const bool has_h = args.kb_h > 0;
-      const size_t hoff = (size_t)row * args.H + (size_t)n_blk * 64 + half * 32;
+      const size_t hoff = (size_t)row * args.H + args.col0 + (size_t)n_blk * 64 + half * 32;
       uint4 hq[4];
       if (has_h && valid) {
         const uint4 *src = reinterpret_cast<const uint4 *>(args.h_prev + hoff);
@@ -475,10 +545,15 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
-      gate_epilogue(t, hq, bias4, args.h_out + hoff, valid);
+      gate_epilogue(t, hq, bias4, args.h_out_peer, args.tp_world, hoff, valid);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
+      if (args.tp_world > 1) {
+        __threadfence_system();
+        __syncwarp();
+        if (lane < args.tp_world) red_release_sys_add(args.signal_peer[lane] + m_tile, 1u);
+      }
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
   }
@@ -507,6 +582,10 @@ struct FcArgs {
   int32_t *chars;
   uint8_t *alive;
   __nv_bfloat16 *onehot;    // [bpad, kx]
+  // tensor parallel: the top layer's hidden buffer arrives in per-rank chunks
+  int tp_world, tp_rank, kb_rank, flag_stride;
+  uint32_t expect_h;
+  const uint32_t *wait_h;
 };
 
 __global__ void __launch_bounds__(F_THREADS, 1)
@@ -540,10 +619,18 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x)
-        for (int kb = 0; kb < args.kb; ++kb) {
+        for (int j = 0; j < args.kb; ++j) {
+          int kb = j;
+          if (args.tp_world > 1) {
+            int src;
+            kb = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
+            if (src != args.tp_rank && j % args.kb_rank == 0)
+              tp_wait_counter(args.wait_h + src * args.flag_stride + tile, args.expect_h);
+          }
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t *sa = smem + stage * F_STAGE_BYTES;
           mbar_expect_tx(&full_bar[stage], TC_A_BYTES + b_bytes);
+          if (args.tp_world > 1) fence_proxy_async();
           tma_load_2d(sa, &map_h, &full_bar[stage], kb * TC_BLOCK_K, tile * kTileM);
           tma_load_2d(sa + TC_A_BYTES, &map_w, &full_bar[stage], kb * TC_BLOCK_K, 0);
           if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
@@ -660,20 +747,22 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
 }
 
 // ------------------------------------------------------------- init / packing
-// fp32 [3][H][K] (gate-stacked r,z,n as in the file) -> bf16 [H/64][3][64][K]
+// A rank packs only the hidden units it owns: [unit0, unit0 + Hs) of H (Hs == H
+// without tensor parallelism).
+// fp32 [3][H][K] (gate-stacked r,z,n as in the file) -> bf16 [Hs/64][3][64][K]
 // with the gate order of the packed block given by (g0,g1,g2).
 __global__ void pack_gate_weights_kernel(const float *__restrict__ src,
                                          __nv_bfloat16 *__restrict__ dst, int H,
-                                         int K, int g0, int g1, int g2) {
+                                         int Hs, int unit0, int K, int g0, int g1, int g2) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  size_t total = (size_t)3 * H * K;
+  size_t total = (size_t)3 * Hs * K;
   if (idx >= total) return;
   int k = (int)(idx % K);
   size_t prow = idx / K;  // packed row
   int jb = (int)(prow / 192), rem = (int)(prow % 192);
   int slot = rem / 64, u = rem % 64;
   int g = slot == 0 ? g0 : (slot == 1 ? g1 : g2);
-  dst[idx] = __float2bfloat16_rn(src[((size_t)g * H + jb * 64 + u) * K + k]);
+  dst[idx] = __float2bfloat16_rn(src[((size_t)g * H + unit0 + jb * 64 + u) * K + k]);
 }
 
 __global__ void to_bf16_kernel(const float *__restrict__ src,
@@ -688,15 +777,15 @@ __global__ void pack_t0_kernel(const float *__restrict__ t0_raw,
                                const float *__restrict__ b_ih,
                                const float *__restrict__ b_hh,
                                __nv_bfloat16 *__restrict__ t0w, int C, int H,
-                               int kx) {
+                               int Hs, int unit0, int kx) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (size_t)3 * H * kx) return;
+  if (idx >= (size_t)3 * Hs * kx) return;
   int c = (int)(idx % kx);
   size_t prow = idx / kx;
   int jb = (int)(prow / 192), rem = (int)(prow % 192);
   int slot = rem / 64, u = rem % 64;
   int g = slot == 0 ? 2 : slot - 1;  // slots (n, r, z) <- gates (2, 0, 1)
-  int i = jb * 64 + u;
+  int i = unit0 + jb * 64 + u;
   float v = 0.0f;
   if (c < C) {
     v = t0_raw[(size_t)c * 3 * H + g * H + i] + b_ih[g * H + i];
@@ -709,11 +798,12 @@ __global__ void pack_t0_kernel(const float *__restrict__ t0_raw,
 // Layer 0 folds q=0..2 into the T0 table, so they are zero there.
 __global__ void pack_bias_kernel(const float *__restrict__ b_ih,
                                  const float *__restrict__ b_hh,
-                                 float *__restrict__ out, int H, int folded) {
+                                 float *__restrict__ out, int H, int Hs, int unit0,
+                                 int folded) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= 4 * H) return;
+  if (idx >= 4 * Hs) return;
   int jb = idx / 256, q = (idx % 256) / 64, u = idx % 64;
-  int i = jb * 64 + u;
+  int i = unit0 + jb * 64 + u;
   float v;
   if (q == 0) v = folded ? 0.0f : b_ih[2 * H + i];
   else if (q == 1) v = folded ? 0.0f : b_ih[i] + b_hh[i];
@@ -743,6 +833,21 @@ __global__ void tc_signal_done_kernel(uint32_t *flag, uint32_t value) {
   st_release_sys(flag, value);
 }
 
+// Tensor-parallel call fence.  wait: every peer has finished generate number
+// `epoch` (its kernels no longer read or write our buffers).  signal: tell
+// every peer that we have.
+__global__ void tp_wait_epoch_kernel(const uint32_t *sync_local, int world, uint32_t epoch) {
+  if ((int)threadIdx.x < world)
+    while ((int32_t)(ld_acquire_sys(sync_local + threadIdx.x) - epoch) < 0) __nanosleep(200);
+}
+struct TpPeers { uint32_t *p[8]; };
+__global__ void tp_signal_epoch_kernel(TpPeers sync_slot, int world, uint32_t epoch) {
+  if ((int)threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(sync_slot.p[threadIdx.x], epoch);
+  }
+}
+
 template <typename T>
 static int tc_alloc(b200gru_model *m, T **out, size_t count) {
   void *p = nullptr;
@@ -757,9 +862,61 @@ static int tc_alloc(b200gru_model *m, T **out, size_t count) {
   return 0;
 }
 
+// Layout of the peer-visible region a tensor-parallel rank exposes:
+//   h[l][pp]            L*2 buffers of [bpad, H] bf16 (full width)
+//   counters[l][pp]     [world][mt_max] uint32 per buffer
+//   sync                [world] uint32 (call fence)
+static size_t tp_h_bytes(const b200gru_model *m) {
+  return (size_t)m->bpad * m->cfg.hidden * sizeof(__nv_bfloat16);
+}
+static size_t tp_counter_bytes(const b200gru_model *m) {
+  return (size_t)m->tp_world * (m->bpad / kTileM) * sizeof(uint32_t);
+}
+size_t tp_shared_bytes(const b200gru_model *m) {
+  const int L = m->cfg.num_layers;
+  size_t b = (size_t)L * 2 * tp_h_bytes(m);
+  b += (size_t)L * 2 * ((tp_counter_bytes(m) + 255) / 256 * 256);
+  b += 256;
+  return b;
+}
+
+static int make_h_maps(b200gru_model *m) {
+  for (int l = 0; l < m->cfg.num_layers; ++l)
+    for (int pp = 0; pp < 2; ++pp)
+      if (int rc = make_tmap_bf16_2d(&m->tc[l].map_h[pp], m->tc[l].h[pp], (uint64_t)m->bpad,
+                                     (uint64_t)m->cfg.hidden, kTileM, 64))
+        return rc;
+  return 0;
+}
+
+int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
+  B200_REQUIRE(m->tp_world > 1, "model was not created for tensor parallelism");
+  const int L = m->cfg.num_layers;
+  const size_t hb = tp_h_bytes(m);
+  const size_t cb = (tp_counter_bytes(m) + 255) / 256 * 256;
+  const size_t off_cnt = (size_t)L * 2 * hb;
+  const size_t off_sync = off_cnt + (size_t)L * 2 * cb;
+  for (int r = 0; r < m->tp_world; ++r) {
+    uint8_t *base = static_cast<uint8_t *>(r == m->tp_rank ? local_base : peer_bases[r]);
+    B200_REQUIRE(base, "peer base %d is null", r);
+    for (int l = 0; l < L; ++l)
+      for (int pp = 0; pp < 2; ++pp) {
+        m->tp_h[r][l][pp] = reinterpret_cast<__nv_bfloat16 *>(base + (size_t)(l * 2 + pp) * hb);
+        m->tp_cnt[r][l][pp] = reinterpret_cast<uint32_t *>(base + off_cnt + (size_t)(l * 2 + pp) * cb);
+      }
+    m->tp_sync[r] = reinterpret_cast<uint32_t *>(base + off_sync);
+  }
+  for (int l = 0; l < L; ++l)
+    for (int pp = 0; pp < 2; ++pp) m->tc[l].h[pp] = m->tp_h[m->tp_rank][l][pp];
+  if (int rc = make_h_maps(m)) return rc;
+  m->tp_bound = true;
+  return 0;
+}
+
 int tc_prepare(b200gru_model *m) {
   const b200gru_config &c = m->cfg;
   const int H = c.hidden, C = c.num_char, L = c.num_layers;
+  const int Hs = H / m->tp_world, unit0 = m->tp_rank * Hs;
   LayoutIndex ix(L);
   const unsigned TPB = 256;
   auto blocks = [&](size_t n) { return (unsigned)((n + TPB - 1) / TPB); };
@@ -771,50 +928,45 @@ int tc_prepare(b200gru_model *m) {
   B200_CUDA(cudaMemset(m->onehot, 0, sizeof(__nv_bfloat16) * (size_t)m->bpad * kx));
   if (int rc = make_tmap_bf16_2d(&m->map_onehot, m->onehot, (uint64_t)m->bpad, kx, kTileM, 64))
     return rc;
-  if (int rc = tc_alloc(m, &m->t0w, (size_t)3 * H * kx)) return rc;
-  pack_t0_kernel<<<blocks((size_t)3 * H * kx), TPB>>>(
-      m->t0_raw, m->P(ix.b_i(0, 0)), m->P(ix.b_h(0, 0)), m->t0w, C, H, kx);
-  if (int rc = make_tmap_bf16_2d(&m->map_t0w, m->t0w, 3 * (uint64_t)H, kx, 192, 64))
-    return rc;
+  if (int rc = tc_alloc(m, &m->t0w, (size_t)3 * Hs * kx)) return rc;
+  pack_t0_kernel<<<blocks((size_t)3 * Hs * kx), TPB>>>(
+      m->t0_raw, m->P(ix.b_i(0, 0)), m->P(ix.b_h(0, 0)), m->t0w, C, H, Hs, unit0, kx);
+  if (int rc = make_tmap_bf16_2d(&m->map_t0w, m->t0w, 3 * (uint64_t)Hs, kx, 192, 64)) return rc;
+  if (int rc = make_tmap_bf16_2d(&m->map_t0w_p, m->t0w, 3 * (uint64_t)Hs, kx, 96, 64)) return rc;
 
   for (int l = 0; l < L; ++l) {
     TcLayer &t = m->tc[l];
-    const size_t wn = (size_t)3 * H * H;
+    const size_t wn = (size_t)3 * Hs * H;
     if (l > 0) {
       if (int rc = tc_alloc(m, &t.w_ih, wn)) return rc;
       // x-part column order [n_i | r | z]
-      pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_i(l, 0)), t.w_ih, H, H, 2, 0, 1);
-      if (int rc = make_tmap_bf16_2d(&t.map_w_ih, t.w_ih, 3 * (uint64_t)H, H, 192, 64))
-        return rc;
+      pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_i(l, 0)), t.w_ih, H, Hs, unit0, H,
+                                                    2, 0, 1);
+      if (int rc = make_tmap_bf16_2d(&t.map_w_ih, t.w_ih, 3 * (uint64_t)Hs, H, 192, 64)) return rc;
+      if (int rc = make_tmap_bf16_2d(&t.map_w_ih_p, t.w_ih, 3 * (uint64_t)Hs, H, 96, 64)) return rc;
     }
     if (int rc = tc_alloc(m, &t.w_hh, wn)) return rc;
     // h-part column order [r | z | n_h]
-    pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_h(l, 0)), t.w_hh, H, H, 0, 1, 2);
-    if (int rc = make_tmap_bf16_2d(&t.map_w_hh, t.w_hh, 3 * (uint64_t)H, H, 192, 64))
-      return rc;
-    if (int rc = tc_alloc(m, &t.bias, (size_t)4 * H)) return rc;
-    pack_bias_kernel<<<blocks((size_t)4 * H), TPB>>>(m->P(ix.b_i(l, 0)), m->P(ix.b_h(l, 0)),
-                                                     t.bias, H, l == 0 ? 1 : 0);
-    for (int pp = 0; pp < 2; ++pp) {
-      if (int rc = tc_alloc(m, &t.h[pp], (size_t)m->bpad * H)) return rc;
-      B200_CUDA(cudaMemset(t.h[pp], 0, sizeof(__nv_bfloat16) * (size_t)m->bpad * H));
-      if (int rc = make_tmap_bf16_2d(&t.map_h[pp], t.h[pp], (uint64_t)m->bpad, H, kTileM, 64))
-        return rc;
-    }
+    pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_h(l, 0)), t.w_hh, H, Hs, unit0, H,
+                                                  0, 1, 2);
+    if (int rc = make_tmap_bf16_2d(&t.map_w_hh, t.w_hh, 3 * (uint64_t)Hs, H, 192, 64)) return rc;
+    if (int rc = make_tmap_bf16_2d(&t.map_w_hh_p, t.w_hh, 3 * (uint64_t)Hs, H, 96, 64)) return rc;
+    if (int rc = tc_alloc(m, &t.bias, (size_t)4 * Hs)) return rc;
+    pack_bias_kernel<<<blocks((size_t)4 * Hs), TPB>>>(m->P(ix.b_i(l, 0)), m->P(ix.b_h(l, 0)),
+                                                      t.bias, H, Hs, unit0, l == 0 ? 1 : 0);
+    if (m->tp_world == 1)
+      for (int pp = 0; pp < 2; ++pp) {
+        if (int rc = tc_alloc(m, &t.h[pp], (size_t)m->bpad * H)) return rc;
+        B200_CUDA(cudaMemset(t.h[pp], 0, sizeof(__nv_bfloat16) * (size_t)m->bpad * H));
+      }
   }
+  if (m->tp_world == 1)
+    if (int rc = make_h_maps(m)) return rc;
   if (int rc = tc_alloc(m, &m->w_fc, (size_t)C * H)) return rc;
   to_bf16_kernel<<<blocks((size_t)C * H), TPB>>>(m->P(ix.w_fc()), m->w_fc, (size_t)C * H);
   if (int rc = make_tmap_bf16_2d(&m->map_w_fc, m->w_fc, (uint64_t)C, H, C, 64)) return rc;
   B200_CUDA(cudaGetLastError());
 
-  // CTA-pair variants of the weight maps: each CTA of a pair loads 96 rows
-  if (int rc = make_tmap_bf16_2d(&m->map_t0w_p, m->t0w, 3 * (uint64_t)H, kx, 96, 64)) return rc;
-  for (int l = 0; l < L; ++l) {
-    TcLayer &t = m->tc[l];
-    if (l > 0)
-      if (int rc = make_tmap_bf16_2d(&t.map_w_ih_p, t.w_ih, 3 * (uint64_t)H, H, 96, 64)) return rc;
-    if (int rc = make_tmap_bf16_2d(&t.map_w_hh_p, t.w_hh, 3 * (uint64_t)H, H, 96, 64)) return rc;
-  }
   B200_CUDA(cudaFuncSetAttribute(gru_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  L_SMEM_BYTES));
   B200_CUDA(cudaFuncSetAttribute(gru_layer_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -840,10 +992,20 @@ static int num_sms(int device) {
 int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
   const b200gru_config &c = m->cfg;
   const int H = c.hidden, C = c.num_char, T = c.max_len, L = c.num_layers;
+  const int W = m->tp_world, R = m->tp_rank;
+  const int Hs = H / W;
   const int sms = num_sms(m->device);
   int launches = 0;
   const int m_tiles = (n + kTileM - 1) / kTileM;
   const int rows = m_tiles * kTileM;
+  const int mt_max = m->bpad / kTileM;
+  const uint32_t per_round = (uint32_t)(Hs / kUnitBlock) * L_EPI_WARPS;  // counter bumps per m-tile
+  if (W > 1) {
+    if (!m->tp_bound) return fail(B200GRU_ERR_STATE, "tensor-parallel model: call b200gru_tp_bind first");
+    // nobody may touch our buffers for this call until every peer is done with the last one
+    tp_wait_epoch_kernel<<<1, 32, 0, s>>>(m->tp_sync[R], W, m->tp_epoch);
+    ++launches;
+  }
   {
     size_t total = (size_t)rows * m->kx;
     tc_init_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(
@@ -855,10 +1017,26 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
     for (int l = 0; l < L; ++l) {
       TcLayer &t = m->tc[l];
       LayerArgs a{};
-      a.n = n; a.m_tiles = m_tiles; a.n_blocks = H / kUnitBlock;
+      a.n = n; a.m_tiles = m_tiles; a.n_blocks = Hs / kUnitBlock;
       a.kb_x = (l == 0 ? m->kx : H) / TC_BLOCK_K;
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
       a.H = H; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
+      a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.x_full = l > 0;
+      a.col0 = R * Hs; a.flag_stride = mt_max;
+      a.h_out_peer[0] = t.h[wr];
+      if (W > 1) {
+        m->tp_rounds[l][wr] += 1;  // this launch is one more write round of buffer (l, wr)
+        for (int r = 0; r < W; ++r) {
+          a.h_out_peer[r] = m->tp_h[r][l][wr];
+          a.signal_peer[r] = m->tp_cnt[r][l][wr] + (size_t)R * mt_max;
+        }
+        a.wait_h = m->tp_cnt[R][l][rd];
+        a.expect_h = m->tp_rounds[l][rd] * per_round;
+        if (l > 0) {
+          a.wait_x = m->tp_cnt[R][l - 1][wr];
+          a.expect_x = m->tp_rounds[l - 1][wr] * per_round;
+        }
+      }
       const int tiles = a.m_tiles * a.n_blocks;
       if (m->use_pairs && m_tiles >= 2) {
         // 256-name tiles on CTA pairs (clusters of 2, one pair per TPC)
@@ -893,8 +1071,20 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
     a.b_fc = m->b_fc; a.logits = m->debug_logits ? m->logits : nullptr;
     a.rfloats = io->rfloats; a.output = io->output;
     a.chars = m->chars; a.alive = m->alive; a.onehot = m->onehot;
+    a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.flag_stride = mt_max;
+    if (W > 1) {
+      a.wait_h = m->tp_cnt[R][L - 1][wr];
+      a.expect_h = m->tp_rounds[L - 1][wr] * per_round;
+    }
     const int grid = m_tiles < sms ? m_tiles : sms;
     fc_sample_kernel<<<grid, F_THREADS, F_SMEM_BYTES, s>>>(m->tc[L - 1].map_h[wr], m->map_w_fc, a);
+    ++launches;
+  }
+  if (W > 1) {
+    m->tp_epoch += 1;
+    TpPeers peers{};
+    for (int r = 0; r < W; ++r) peers.p[r] = m->tp_sync[r] + R;
+    tp_signal_epoch_kernel<<<1, 32, 0, s>>>(peers, W, m->tp_epoch);
     ++launches;
   }
   if (io->done_flag) {

@@ -65,6 +65,15 @@ struct b200gru_model {
   CUtensorMap map_w_fc;
   const float *b_fc = nullptr;    // into params
 
+  // --- tensor parallelism over the hidden dimension (tp_world == 1: off)
+  int tp_world = 1, tp_rank = 0;
+  bool tp_bound = false;
+  uint32_t tp_epoch = 0;                                   // completed generate calls
+  uint32_t tp_rounds[B200GRU_MAX_LAYERS][2] = {};          // write rounds per hidden buffer
+  __nv_bfloat16 *tp_h[8][B200GRU_MAX_LAYERS][2] = {};      // [rank][layer][pp] hidden buffers
+  uint32_t *tp_cnt[8][B200GRU_MAX_LAYERS][2] = {};         // [rank][layer][pp] -> [src][m_tile]
+  uint32_t *tp_sync[8] = {};                               // [rank] -> [src] call-fence words
+
   const float *P(int k) const { return params + lay[k].offset; }
 };
 
@@ -81,6 +90,8 @@ int gru_cell_fp32_run(const float *x, const float *h_in, const float *w_ih,
 // tensor-core path (gru_tc_sm100.cu)
 int tc_prepare(b200gru_model *m);
 int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s);
+size_t tp_shared_bytes(const b200gru_model *m);
+int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases);
 // TMA descriptor helper (tma_host.cu)
 int make_tmap_bf16_2d(CUtensorMap *map, const void *base, uint64_t rows,
                       uint64_t cols, uint32_t box_rows, uint32_t box_cols);

@@ -44,7 +44,7 @@ class NameGenerator:
     """
 
     def __init__(self, cfg: GRUConfig, params, device: int | None = None, max_batch: int = 4096,
-                 mode: str = "tc", comm=None):
+                 mode: str = "tc", comm=None, tp_rank: int = 0, tp_world: int = 1):
         if not torch.cuda.is_available():
             raise RuntimeError("NameGenerator needs a CUDA device (use models.oracle / TorchNameGen on CPU)")
         self.cfg = cfg
@@ -60,8 +60,10 @@ class NameGenerator:
         self._lib = _native.lib()
         handle = ctypes.c_void_p()
         c = cfg.to_c()
-        _native.check(self._lib.b200gru_model_create(ctypes.byref(c), params.data_ptr(), self.device,
-                                                     self.max_batch, ctypes.byref(handle)), "model_create")
+        self.tp_rank, self.tp_world = int(tp_rank), int(tp_world)
+        _native.check(self._lib.b200gru_model_create_tp(ctypes.byref(c), params.data_ptr(), self.device,
+                                                        self.max_batch, self.tp_rank, self.tp_world,
+                                                        ctypes.byref(handle)), "model_create")
         self._h = handle
         dev = torch.device("cuda", self.device)
         # device-side staging for the single-process path (root == this rank)

@@ -5,6 +5,9 @@ def __getattr__(name):  # lazy: dp/symm import torch.distributed
     if name == "DPContext":
         from .dp import DPContext
         return DPContext
+    if name == "TPContext":
+        from .tp import TPContext
+        return TPContext
     if name == "SymmBuffer":
         from .symm import SymmBuffer
         return SymmBuffer

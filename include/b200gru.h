@@ -112,6 +112,22 @@ typedef struct b200gru_model b200gru_model; /* opaque */
  * ref:409-468, 583-612). */
 int b200gru_model_create(const b200gru_config *cfg, const float *params,
                          int device, int max_batch, b200gru_model **out);
+/* Tensor-parallel variant (not in the reference, which replicates all weights
+ * on every rank, ref:370-407): the hidden dimension of every layer is split
+ * over `tp_world` GPUs; this rank packs and keeps only the weight rows of its
+ * own hidden units.  Hidden-state buffers are full width on every rank and
+ * live in a peer-visible region the caller provides:
+ *   1. create on every rank, 2. allocate b200gru_tp_shared_bytes() with
+ *   b200gru_symm_alloc and exchange handles, 3. b200gru_tp_bind().
+ * Each layer kernel then stores its slice of h' into every rank's buffer
+ * (NVLink P2P) and the next kernel's TMA producer consumes remote K-chunks as
+ * their counters arrive: the all-gather is fused into the GEMM's K loop. */
+int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
+                            int device, int max_batch, int tp_rank,
+                            int tp_world, b200gru_model **out);
+size_t b200gru_tp_shared_bytes(const b200gru_model *m);
+/* peer_bases[r] = mapped address of rank r's region (entry tp_rank ignored). */
+int b200gru_tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases);
 /* namegen_finalize() equivalent (ref:897-1033). */
 int b200gru_model_destroy(b200gru_model *m);
 int64_t b200gru_model_device_bytes(const b200gru_model *m);

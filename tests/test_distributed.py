@@ -65,3 +65,15 @@ def test_real_ranks_p2p(method):
     r = _torchrun(world, "gpu", 1001, method, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("GPU_DP_OK") == 2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("hidden,n", [(256, 600), (512, 130)])
+def test_tensor_parallel_matches_single_gpu(hidden, n):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 2 if hidden == 256 else min(4, torch.cuda.device_count())
+    world = max(w for w in (1, 2, 4, 8) if w <= world and hidden % (64 * w) == 0)
+    r = _torchrun(world, "tp", n, hidden, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "GPU_TP_OK" in r.stdout
