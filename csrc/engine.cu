@@ -149,6 +149,7 @@ int b200gru_model_destroy(b200gru_model *m) {
   if (!m) return 0;
   DeviceGuard guard(m->device);
   cudaError_t first = cudaDeviceSynchronize();
+  for (cudaEvent_t e : m->trace_ev) cudaEventDestroy(e);
   for (void *p : m->allocs) {
     cudaError_t e = cudaFree(p);
     if (first == cudaSuccess) first = e;
@@ -197,6 +198,26 @@ int b200gru_model_set_debug(b200gru_model *m, int logits_tap) {
   B200_REQUIRE(m, "null model");
   m->debug_logits = logits_tap != 0;
   return 0;
+}
+
+int b200gru_model_set_trace(b200gru_model *m, int on) {
+  B200_REQUIRE(m, "null model");
+  m->trace_on = on != 0;
+  return 0;
+}
+
+// Spans of the last traced generate: fills ms[i] / names[i], returns the count.
+int b200gru_model_get_trace(b200gru_model *m, float *ms, const char **names, int max_spans) {
+  B200_REQUIRE(m && ms && names, "null argument");
+  DeviceGuard guard(m->device);
+  const int spans = m->trace_used > 0 ? m->trace_used - 1 : 0;
+  if (spans > 0) B200_CUDA(cudaEventSynchronize(m->trace_ev[m->trace_used - 1]));
+  int n = spans < max_spans ? spans : max_spans;
+  for (int i = 0; i < n; ++i) {
+    B200_CUDA(cudaEventElapsedTime(&ms[i], m->trace_ev[i], m->trace_ev[i + 1]));
+    names[i] = i < (int)m->trace_names.size() ? m->trace_names[i] : "?";
+  }
+  return n;
 }
 
 int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,

@@ -55,8 +55,14 @@ constexpr int L_EPI_WARPS = 8;
 constexpr int L_THREADS = (4 + L_EPI_WARPS) * 32;
 constexpr int L_B_BYTES = 192 * 128;         // 24 KB
 constexpr int L_STAGE_BYTES = TC_A_BYTES + L_B_BYTES;
-constexpr int L_STAGES = 5;
-constexpr int L_SMEM_BYTES = L_STAGES * L_STAGE_BYTES + 1024 + 256;
+constexpr int L_STAGES = 4;
+constexpr int OUT_TILE_BYTES = kTileM * 128;  // 128 names x 64 units bf16, 128B-swizzled
+// [align slack 1024][stages][barrier block 1024][2 staging tiles]
+constexpr int L_SMEM_BYTES = 1024 + L_STAGES * L_STAGE_BYTES + 1024 + 2 * OUT_TILE_BYTES;
+constexpr int EPI_BAR_ID = 1;                 // named barrier of the epilogue warps
+
+// Output tensor maps: h_out on every tensor-parallel rank ([0] only without TP).
+struct OutMaps { CUtensorMap m[8]; };
 
 struct LayerArgs {
   int n;            // valid names (rows)
@@ -100,11 +106,12 @@ __device__ __forceinline__ void tp_wait_counter(const uint32_t *p, uint32_t expe
 }
 
 // Gate math for one thread's (name, 32 units) slice of a finished tile:
-// t addresses this warp's TMEM lanes at the slice's first n_i column.
+// t addresses this warp's TMEM lanes at the slice's first n_i column.  The bf16
+// result goes to the 128B-swizzled staging tile (row `r`, 16-byte chunks
+// half*4 .. half*4+3), from where one thread TMA-stores the whole tile.
 __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
-                                              const float4 *bias4,
-                                              __nv_bfloat16 *const *dsts, int ndst,
-                                              size_t hoff, bool valid) {
+                                              const float4 *bias4, uint8_t *stage_tile,
+                                              int r, int half) {
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     uint32_t vn[16], vr[16], vz[16], vh[16];
@@ -133,9 +140,9 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
         const int i = q * 4 + e;
         const uint32_t w = hw[i >> 1];
         const float hp = __uint_as_float((i & 1) ? (w & 0xFFFF0000u) : (w << 16));
-        const float r = sigmoid_approx(__uint_as_float(vr[i]) + br[e]);
+        const float rr = sigmoid_approx(__uint_as_float(vr[i]) + br[e]);
         const float z = sigmoid_approx(__uint_as_float(vz[i]) + bz[e]);
-        const float nn = tanh_approx(fmaf(r, __uint_as_float(vh[i]) + bh[e],
+        const float nn = tanh_approx(fmaf(rr, __uint_as_float(vh[i]) + bh[e],
                                           __uint_as_float(vn[i]) + bi[e]));
         // h' = (1-z)*n + z*h  ==  n + z*(h - n)     (ref:752-763)
         hn[e] = fmaf(z, hp - nn, nn);
@@ -145,15 +152,13 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
       packed[q * 2] = *reinterpret_cast<uint32_t *>(&p0);
       packed[q * 2 + 1] = *reinterpret_cast<uint32_t *>(&p1);
     }
-    if (valid) {
-      const uint4 lo = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-      const uint4 hi = make_uint4(packed[4], packed[5], packed[6], packed[7]);
-      for (int p = 0; p < ndst; ++p) {  // ndst > 1: the all-gather, as P2P stores
-        uint4 *dst = reinterpret_cast<uint4 *>(dsts[p] + hoff + ch * 16);
-        dst[0] = lo;
-        dst[1] = hi;
-      }
-    }
+    // chunks c0, c0+1 of this row, XOR-swizzled like CU_TENSOR_MAP_SWIZZLE_128B
+    const int c0 = half * 4 + ch * 2;
+    uint8_t *rowp = stage_tile + r * 128;
+    *reinterpret_cast<uint4 *>(rowp + (((c0) ^ (r & 7)) << 4)) =
+        make_uint4(packed[0], packed[1], packed[2], packed[3]);
+    *reinterpret_cast<uint4 *>(rowp + (((c0 + 1) ^ (r & 7)) << 4)) =
+        make_uint4(packed[4], packed[5], packed[6], packed[7]);
   }
   // re-zero this warp's n_h columns before the stage goes back to the MMAs
   uint32_t zero[16];
@@ -164,12 +169,46 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
   tmem_st_wait();
 }
 
+// Tail of a tile's epilogue, run by every epilogue thread.  `issuer` (one
+// thread per CTA) TMA-stores the staged tile to every destination and, under
+// tensor parallelism, publishes the PREVIOUS tile — whose stores have had a
+// whole tile time to land — by bumping its counter on every rank.
+struct EpiState { int prev_m_tile; };
+__device__ __forceinline__ void epilogue_store_tile(const OutMaps &outs, const LayerArgs &args,
+                                                    uint8_t *stage_tile, int col, int m_tile,
+                                                    bool issuer, EpiState &st) {
+  fence_proxy_async_smem();                       // generic smem writes -> async proxy
+  named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);   // the staged tile is complete
+  if (issuer) {
+    for (int d = 0; d < args.tp_world; ++d)
+      tma_store_2d(&outs.m[d], stage_tile, col, m_tile * kTileM);
+    tma_store_commit();
+    if (args.tp_world > 1 && st.prev_m_tile >= 0) {
+      tma_store_wait<1>();                        // everything but the group just committed
+      fence_proxy_async();
+      for (int d = 0; d < args.tp_world; ++d)
+        red_release_sys_add(args.signal_peer[d] + st.prev_m_tile, 1u);
+    }
+    st.prev_m_tile = m_tile;
+  }
+}
+__device__ __forceinline__ void epilogue_finish(const LayerArgs &args, bool issuer, EpiState &st) {
+  if (issuer) {
+    tma_store_wait<0>();                          // smem must outlive the reads; peers must see data
+    if (args.tp_world > 1 && st.prev_m_tile >= 0) {
+      fence_proxy_async();
+      for (int d = 0; d < args.tp_world; ++d)
+        red_release_sys_add(args.signal_peer[d] + st.prev_m_tile, 1u);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(L_THREADS, 1)
 gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
                  const __grid_constant__ CUtensorMap map_h,
                  const __grid_constant__ CUtensorMap map_wx,
                  const __grid_constant__ CUtensorMap map_wh,
-                 const LayerArgs args) {
+                 const __grid_constant__ OutMaps outs, const LayerArgs args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -244,11 +283,12 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
         if (args.tp_world > 1 && (!is_x || args.x_full)) {
           int src;
           kblk = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
-          if (src != args.tp_rank) {
+          if (src != args.tp_rank && j % args.kb_rank == 0) {
+            // first k-block of a remote rank's chunk: acquire its counter once,
+            // then one proxy fence orders the TMA reads of the whole chunk
+            tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
+                            is_x ? args.expect_x : args.expect_h);
             tp_fence = true;
-            if (j % args.kb_rank == 0)
-              tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
-                              is_x ? args.expect_x : args.expect_h);
           }
         }
         mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -312,13 +352,18 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     int acc_stage = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    uint8_t *stage_out = smem + L_STAGES * L_STAGE_BYTES + 1024;  // after the barrier block
+    const bool issuer = (warp == 4 && lane == 0);
+    EpiState est{-1};
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int m_tile = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
-      const int row = m_tile * kTileM + quarter * 32 + lane;
-      const bool valid = row < args.n;
+      const int r = quarter * 32 + lane;
+      const int row = m_tile * kTileM + r;
       const bool has_h = args.kb_h > 0;
-      const size_t hoff = (size_t)row * args.H + args.col0 + (size_t)n_blk * 64 + half * 32;
+      const int col = args.col0 + n_blk * 64;
+      const size_t hoff = (size_t)row * args.H + col + half * 32;
       // previous hidden for this thread's 32 units: issue the loads before
       // waiting on the accumulator so their latency hides behind the MMAs
       uint4 hq[4];
@@ -332,21 +377,22 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       }
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
+      uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
+      // the TMA stores that read this staging buffer two tiles ago are done
+      if (issuer) tma_store_wait_read<1>();
+      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
 
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
-      gate_epilogue(t, hq, bias4, args.h_out_peer, args.tp_world, hoff, valid);
+      gate_epilogue(t, hq, bias4, stage_tile, r, half);
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
-      if (args.tp_world > 1) {  // publish this warp's slice of (m_tile, n_blk)
-        __threadfence_system();
-        __syncwarp();
-        if (lane < args.tp_world) red_release_sys_add(args.signal_peer[lane] + m_tile, 1u);
-      }
+      if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);  // TMEM stage back to the MMAs
+      epilogue_store_tile(outs, args, stage_tile, col, m_tile, issuer, est);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
+    epilogue_finish(args, issuer, est);
   }
 
   tc_fence_before();
@@ -369,15 +415,15 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
 //   tcgen05.commit multicasts to the `empty` / tmem_full barriers of both CTAs.
 constexpr int P_B_BYTES = 96 * 128;          // 12 KB: this CTA's half of B
 constexpr int P_STAGE_BYTES = TC_A_BYTES + P_B_BYTES;
-constexpr int P_STAGES = 7;
-constexpr int P_SMEM_BYTES = P_STAGES * P_STAGE_BYTES + 1024 + 256;
+constexpr int P_STAGES = 6;
+constexpr int P_SMEM_BYTES = 1024 + P_STAGES * P_STAGE_BYTES + 1024 + 2 * OUT_TILE_BYTES;
 
 __global__ void __launch_bounds__(L_THREADS, 1)
 gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
                       const __grid_constant__ CUtensorMap map_h,
                       const __grid_constant__ CUtensorMap map_wx,
                       const __grid_constant__ CUtensorMap map_wh,
-                      const LayerArgs args) {
+                      const __grid_constant__ OutMaps outs, const LayerArgs args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -454,11 +500,12 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
         if (args.tp_world > 1 && (!is_x || args.x_full)) {
           int src;
           kblk = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
-          if (src != args.tp_rank) {
+          if (src != args.tp_rank && j % args.kb_rank == 0) {
+            // first k-block of a remote rank's chunk: acquire its counter once,
+            // then one proxy fence orders the TMA reads of the whole chunk
+            tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
+                            is_x ? args.expect_x : args.expect_h);
             tp_fence = true;
-            if (j % args.kb_rank == 0)
-              tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
-                              is_x ? args.expect_x : args.expect_h);
           }
         }
         mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -523,16 +570,21 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     int acc_stage = 0;
     uint32_t acc_phase = 0;
-    for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+    uint8_t *stage_out = smem + P_STAGES * P_STAGE_BYTES + 1024;  // after the barrier block
+    const bool issuer = (warp == 4 && lane == 0);
+    EpiState est{-1};
+    int it = 0;
+    for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
       const int m2 = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
       const int m_tile = m2 * 2 + (int)rank;
-      const int row = m_tile * kTileM + quarter * 32 + lane;
-      const bool valid = row < args.n;
+      const int r = quarter * 32 + lane;
+      const int row = m_tile * kTileM + r;
       const bool has_h = args.kb_h > 0;
-      const size_t hoff = (size_t)row * args.H + args.col0 + (size_t)n_blk * 64 + half * 32;
+      const int col = args.col0 + n_blk * 64;
+      const size_t hoff = (size_t)row * args.H + col + half * 32;
       uint4 hq[4];
-      if (has_h && valid) {
+      if (has_h) {
         const uint4 *src = reinterpret_cast<const uint4 *>(args.h_prev + hoff);
 #pragma unroll
         for (int i = 0; i < 4; ++i) hq[i] = src[i];
@@ -542,20 +594,21 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       }
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
+      uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
+      if (issuer) tma_store_wait_read<1>();
+      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
+
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
-      gate_epilogue(t, hq, bias4, args.h_out_peer, args.tp_world, hoff, valid);
+      gate_epilogue(t, hq, bias4, stage_tile, r, half);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
-      if (args.tp_world > 1) {
-        __threadfence_system();
-        __syncwarp();
-        if (lane < args.tp_world) red_release_sys_add(args.signal_peer[lane] + m_tile, 1u);
-      }
+      epilogue_store_tile(outs, args, stage_tile, col, m_tile, issuer, est);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
+    epilogue_finish(args, issuer, est);
   }
 
   tc_fence_before();
@@ -624,13 +677,14 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
           if (args.tp_world > 1) {
             int src;
             kb = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
-            if (src != args.tp_rank && j % args.kb_rank == 0)
+            if (src != args.tp_rank && j % args.kb_rank == 0) {
               tp_wait_counter(args.wait_h + src * args.flag_stride + tile, args.expect_h);
+              fence_proxy_async();
+            }
           }
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t *sa = smem + stage * F_STAGE_BYTES;
           mbar_expect_tx(&full_bar[stage], TC_A_BYTES + b_bytes);
-          if (args.tp_world > 1) fence_proxy_async();
           tma_load_2d(sa, &map_h, &full_bar[stage], kb * TC_BLOCK_K, tile * kTileM);
           tma_load_2d(sa + TC_A_BYTES, &map_w, &full_bar[stage], kb * TC_BLOCK_K, 0);
           if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
@@ -909,6 +963,13 @@ int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
   for (int l = 0; l < L; ++l)
     for (int pp = 0; pp < 2; ++pp) m->tc[l].h[pp] = m->tp_h[m->tp_rank][l][pp];
   if (int rc = make_h_maps(m)) return rc;
+  // store maps over every rank's copy of every hidden buffer (peer addresses)
+  for (int r = 0; r < m->tp_world; ++r)
+    for (int l = 0; l < L; ++l)
+      for (int pp = 0; pp < 2; ++pp)
+        if (int rc = make_tmap_bf16_2d(&m->tp_map_h[r][l][pp], m->tp_h[r][l][pp], (uint64_t)m->bpad,
+                                       (uint64_t)m->cfg.hidden, kTileM, 64))
+          return rc;
   m->tp_bound = true;
   return 0;
 }
@@ -999,18 +1060,21 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
   const int m_tiles = (n + kTileM - 1) / kTileM;
   const int rows = m_tiles * kTileM;
   const int mt_max = m->bpad / kTileM;
-  const uint32_t per_round = (uint32_t)(Hs / kUnitBlock) * L_EPI_WARPS;  // counter bumps per m-tile
+  const uint32_t per_round = (uint32_t)(Hs / kUnitBlock);  // counter bumps per (source, m-tile)
+  m->trace_begin(s);
   if (W > 1) {
     if (!m->tp_bound) return fail(B200GRU_ERR_STATE, "tensor-parallel model: call b200gru_tp_bind first");
     // nobody may touch our buffers for this call until every peer is done with the last one
     tp_wait_epoch_kernel<<<1, 32, 0, s>>>(m->tp_sync[R], W, m->tp_epoch);
     ++launches;
+    m->trace_mark("tp_wait_epoch", s);
   }
   {
     size_t total = (size_t)rows * m->kx;
     tc_init_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(
         m->chars, m->alive, m->onehot, n, rows, m->kx, c.sos);
     ++launches;
+    m->trace_mark("init", s);
   }
   for (int step = 0; step < T; ++step) {
     const int rd = step & 1, wr = rd ^ 1;  // ping-pong hidden buffers
@@ -1024,10 +1088,13 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
       a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.x_full = l > 0;
       a.col0 = R * Hs; a.flag_stride = mt_max;
       a.h_out_peer[0] = t.h[wr];
+      OutMaps outs;
+      outs.m[0] = t.map_h[wr];
       if (W > 1) {
         m->tp_rounds[l][wr] += 1;  // this launch is one more write round of buffer (l, wr)
         for (int r = 0; r < W; ++r) {
           a.h_out_peer[r] = m->tp_h[r][l][wr];
+          outs.m[r] = m->tp_map_h[r][l][wr];
           a.signal_peer[r] = m->tp_cnt[r][l][wr] + (size_t)R * mt_max;
         }
         a.wait_h = m->tp_cnt[R][l][rd];
@@ -1056,14 +1123,15 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
         cfg.numAttrs = 1;
         B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_pair_kernel,
                                      l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-                                     l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p, a));
+                                     l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p, outs, a));
       } else {
         const int grid = tiles < sms ? tiles : sms;
         gru_layer_kernel<<<grid, L_THREADS, L_SMEM_BYTES, s>>>(
             l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-            l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, a);
+            l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, outs, a);
       }
       ++launches;
+      m->trace_mark(l == 0 ? "layer0" : "layerN", s);
     }
     FcArgs a{};
     a.n = n; a.m_tiles = m_tiles; a.kb = H / TC_BLOCK_K; a.H = H; a.C = C; a.T = T;
@@ -1079,6 +1147,7 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
     const int grid = m_tiles < sms ? m_tiles : sms;
     fc_sample_kernel<<<grid, F_THREADS, F_SMEM_BYTES, s>>>(m->tc[L - 1].map_h[wr], m->map_w_fc, a);
     ++launches;
+    m->trace_mark("fc_sample", s);
   }
   if (W > 1) {
     m->tp_epoch += 1;

@@ -71,8 +71,31 @@ struct b200gru_model {
   uint32_t tp_epoch = 0;                                   // completed generate calls
   uint32_t tp_rounds[B200GRU_MAX_LAYERS][2] = {};          // write rounds per hidden buffer
   __nv_bfloat16 *tp_h[8][B200GRU_MAX_LAYERS][2] = {};      // [rank][layer][pp] hidden buffers
+  CUtensorMap tp_map_h[8][B200GRU_MAX_LAYERS][2];          // TMA store maps over tp_h
   uint32_t *tp_cnt[8][B200GRU_MAX_LAYERS][2] = {};         // [rank][layer][pp] -> [src][m_tile]
   uint32_t *tp_sync[8] = {};                               // [rank] -> [src] call-fence words
+
+  // --- tracing: CUDA events between launches (the reference has no timers at all)
+  bool trace_on = false;
+  std::vector<cudaEvent_t> trace_ev;
+  std::vector<const char *> trace_names;
+  int trace_used = 0;
+  void trace_begin(cudaStream_t s) {
+    trace_used = 0;
+    trace_names.clear();
+    if (trace_on) trace_mark(nullptr, s);
+  }
+  // records an event; `name` labels the span that ENDS here
+  void trace_mark(const char *name, cudaStream_t s) {
+    if (!trace_on) return;
+    if (trace_used == (int)trace_ev.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      trace_ev.push_back(e);
+    }
+    cudaEventRecord(trace_ev[trace_used++], s);
+    if (name) trace_names.push_back(name);
+  }
 
   const float *P(int k) const { return params + lay[k].offset; }
 };

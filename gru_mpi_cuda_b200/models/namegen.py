@@ -112,6 +112,18 @@ class NameGenerator:
         """Make the tensor-core FC kernel store its logits too (slow; tests only)."""
         _native.check(self._lib.b200gru_model_set_debug(self._h, 1 if on else 0))
 
+    def set_trace(self, on: bool = True) -> None:
+        """Record a CUDA event after every launch of the tensor-core path."""
+        _native.check(self._lib.b200gru_model_set_trace(self._h, 1 if on else 0))
+
+    def trace(self) -> list[tuple[str, float]]:
+        """(kernel label, device ms) per launch of the last traced generate."""
+        cap = 256
+        ms = (ctypes.c_float * cap)()
+        names = (ctypes.c_char_p * cap)()
+        n = _native.check(self._lib.b200gru_model_get_trace(self._h, ms, names, cap), "get_trace")
+        return [(names[i].decode(), ms[i]) for i in range(n)]
+
     def debug_logits(self, n: int) -> torch.Tensor:
         """Last step's pre-softmax FC outputs for the first `n` names."""
         out = torch.empty(n, self.cfg.num_char, dtype=torch.float32, device=torch.device("cuda", self.device))

@@ -160,6 +160,13 @@ int b200gru_model_set_debug(b200gru_model *m, int logits_tap);
 int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
                          void *stream);
 
+/* Tracing (absent in the reference): with set_trace(m, 1) the tensor-core
+ * generate records a CUDA event after every launch; get_trace returns the
+ * per-launch device times of the last call (synchronises on its last event). */
+int b200gru_model_set_trace(b200gru_model *m, int on);
+int b200gru_model_get_trace(b200gru_model *m, float *ms, const char **names,
+                            int max_spans);
+
 /* Kernel that spins (ld.acquire.sys) until flags[i] == value for all i<n;
  * rank 0 runs it after its own generate to complete the gather. */
 int b200gru_wait_flags(const uint32_t *flags, int n, uint32_t value,

@@ -119,3 +119,15 @@ def test_eos_stops_and_pads(tiny_cfg):
             out = g.generate(130, r, mode=mode)
             assert (out[:, 0] == tiny_cfg.eos).all(), mode
             assert (out[:, 1:] == 0).all(), mode
+
+
+def test_trace_reports_every_launch(gen_tiny, tiny_cfg):
+    n = 300
+    r = W.random_floats(n * tiny_cfg.max_len, 25)
+    gen_tiny.set_trace(True)
+    gen_tiny.generate(n, r, mode="tc")
+    tr = gen_tiny.trace()
+    gen_tiny.set_trace(False)
+    assert len(tr) == gen_tiny.last_launches == 1 + tiny_cfg.max_len * (tiny_cfg.num_layers + 1)
+    assert [k for k, _ in tr[:4]] == ["init", "layer0", "layerN", "fc_sample"]
+    assert all(t >= 0 for _, t in tr)
