@@ -9,6 +9,8 @@
 // allocated once here, checked, tracked and freed (the reference leaks the
 // file buffer, double-allocates gb_fc ref:571-577, and cudaFree()s a host
 // pointer ref:1017); nothing is allocated in generate.
+#include <cstdlib>
+
 #include "model.hpp"
 #include "sm100_ptx.cuh"
 
@@ -133,8 +135,20 @@ int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
   m->max_batch = max_batch;
   m->tp_rank = tp_rank;
   m->tp_world = tp_world;
+  {
+    const char *e = getenv("B200GRU_TP_FAKE");
+    m->tp_fake = tp_world > 1 && e && e[0] == '1';
+  }
   m->bpad = (max_batch + 2 * kTileM - 1) / (2 * kTileM) * (2 * kTileM);  // whole CTA-pair tiles
   m->lay = build_layout(*cfg);
+  {
+    // pad rows of K=H matrices by 128 bytes: with H a power of two, the 128
+    // rows of a TMA box would otherwise sit exactly 2^k bytes apart
+    const char *e = getenv("B200GRU_LD_PAD");
+    int pad = e ? atoi(e) : 0;
+    if (pad < 0 || pad % 8) pad = 64;
+    m->ldh = cfg->hidden + pad;
+  }
   int rc = create_impl(m, params);
   if (rc) {
     for (void *p : m->allocs) cudaFree(p);

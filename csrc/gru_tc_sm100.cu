@@ -61,8 +61,6 @@ constexpr int OUT_TILE_BYTES = kTileM * 128;  // 128 names x 64 units bf16, 128B
 constexpr int L_SMEM_BYTES = 1024 + L_STAGES * L_STAGE_BYTES + 1024 + 2 * OUT_TILE_BYTES;
 constexpr int EPI_BAR_ID = 1;                 // named barrier of the epilogue warps
 
-// Output tensor maps: h_out on every tensor-parallel rank ([0] only without TP).
-struct OutMaps { CUtensorMap m[8]; };
 
 struct LayerArgs {
   int n;            // valid names (rows)
@@ -70,7 +68,13 @@ struct LayerArgs {
   int n_blocks;     // H / 64
   int kb_x;         // k-blocks (of 64) of the x operand
   int kb_h;         // k-blocks of the recurrent operand (0: h == 0, step 0)
-  int H;
+  // Hidden buffers are stored as column panels: [H / pw panels][bpad rows][pw]
+  // bf16 (pw = H is plain row-major).  Narrow panels make the 128-byte row
+  // segments of a tile sit close together, which is what NVLink P2P writes
+  // need (measured: 128 B segments at 16 KB pitch 180 GB/s, at <= 1 KB pitch
+  // 450-600 GB/s); wide panels spread a TMA box over more L2 slices.
+  int pw_log2;      // log2(panel width in elements)
+  int bpad;         // rows per panel
   const float *bias;            // [H/64, 4, 64]: b_in, b_r, b_z, b_hn
   const __nv_bfloat16 *h_prev;  // [bpad, H]
   __nv_bfloat16 *h_out;         // [bpad, H]
@@ -90,6 +94,18 @@ struct LayerArgs {
   __nv_bfloat16 *h_out_peer[8];     // h_out on every rank ([tp_rank] == h_out)
   uint32_t *signal_peer[8];         // this rank's counter row [m_tile] on every rank
 };
+
+// element offset of (row, col) in a panelled hidden buffer
+__device__ __forceinline__ size_t h_offset(int row, int col, int pw_log2, int bpad) {
+  const int panel = col >> pw_log2;
+  return (((size_t)panel * bpad + row) << pw_log2) + (col & ((1 << pw_log2) - 1));
+}
+// TMA coordinates of the box starting at (row, col)
+__device__ __forceinline__ void h_coords(int row, int col, int pw_log2, int bpad, int *ci, int *co) {
+  const int panel = col >> pw_log2;
+  *ci = col & ((1 << pw_log2) - 1);
+  *co = panel * bpad + row;
+}
 
 // K-block order under tensor parallelism: start with the chunk this rank
 // produced itself, then walk the ring, so remote chunks have time to land.
@@ -169,36 +185,111 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
   tmem_st_wait();
 }
 
-// Tail of a tile's epilogue, run by every epilogue thread.  `issuer` (one
-// thread per CTA) TMA-stores the staged tile to every destination and, under
-// tensor parallelism, publishes the PREVIOUS tile — whose stores have had a
-// whole tile time to land — by bumping its counter on every rank.
+// Tail of a tile's epilogue, run by every epilogue thread (tid = 0..255).
+//  * local copy: one thread TMA-stores the staged tile into this rank's h_out;
+//  * tensor parallel: all 256 threads copy the staged tile to every peer's
+//    h_out with coalesced 16-byte stores (a warp covers four full 128-byte
+//    rows) through the LSU, which keeps far more NVLink writes in flight than
+//    the TMA store path does (measured: ~1 GB/s per SM for remote TMA stores);
+//  * the counter bump that publishes a tile is deferred to the next tile (see
+//    epilogue_publish_prev): by then its stores have had a tile time to land.
 struct EpiState { int prev_m_tile; };
-__device__ __forceinline__ void epilogue_store_tile(const OutMaps &outs, const LayerArgs &args,
+__device__ __forceinline__ void epilogue_store_tile(const CUtensorMap *map_out, const LayerArgs &args,
                                                     uint8_t *stage_tile, int col, int m_tile,
-                                                    bool issuer, EpiState &st) {
+                                                    bool issuer, int tid, EpiState &st) {
   fence_proxy_async_smem();                       // generic smem writes -> async proxy
   named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);   // the staged tile is complete
   if (issuer) {
-    for (int d = 0; d < args.tp_world; ++d)
-      tma_store_2d(&outs.m[d], stage_tile, col, m_tile * kTileM);
+    int ci, co;
+    h_coords(m_tile * kTileM, col, args.pw_log2, args.bpad, &ci, &co);
+    tma_store_2d(map_out, stage_tile, ci, co);
     tma_store_commit();
-    if (args.tp_world > 1 && st.prev_m_tile >= 0) {
-      tma_store_wait<1>();                        // everything but the group just committed
-      fence_proxy_async();
+  }
+  if (args.tp_world > 1) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int idx = tid + j * (L_EPI_WARPS * 32);  // 16-byte chunk of the 16 KB tile
+      const int r = idx >> 3, c = idx & 7;
+      const uint4 v = *reinterpret_cast<const uint4 *>(stage_tile + r * 128 + ((c ^ (r & 7)) << 4));
+      const size_t off = h_offset(m_tile * kTileM + r, col + c * 8, args.pw_log2, args.bpad);
       for (int d = 0; d < args.tp_world; ++d)
-        red_release_sys_add(args.signal_peer[d] + st.prev_m_tile, 1u);
+        if (d != args.tp_rank) *reinterpret_cast<uint4 *>(args.h_out_peer[d] + off) = v;
     }
     st.prev_m_tile = m_tile;
   }
 }
-__device__ __forceinline__ void epilogue_finish(const LayerArgs &args, bool issuer, EpiState &st) {
-  if (issuer) {
-    tma_store_wait<0>();                          // smem must outlive the reads; peers must see data
-    if (args.tp_world > 1 && st.prev_m_tile >= 0) {
-      fence_proxy_async();
-      for (int d = 0; d < args.tp_world; ++d)
-        red_release_sys_add(args.signal_peer[d] + st.prev_m_tile, 1u);
+// Called at the top of the next tile (and once after the last): every thread
+// fences its own remote stores of the previous tile system-wide, the epilogue
+// warps meet, then one thread bumps that tile's counter on every rank.
+__device__ __forceinline__ void epilogue_publish_prev(const LayerArgs &args, bool issuer,
+                                                      EpiState &st, bool need_barrier) {
+  if (args.tp_world > 1 && st.prev_m_tile >= 0) __threadfence_system();
+  if (need_barrier) named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
+  if (issuer && args.tp_world > 1 && st.prev_m_tile >= 0)
+    for (int d = 0; d < args.tp_world; ++d)
+      red_release_sys_add(args.signal_peer[d] + st.prev_m_tile, 1u);
+}
+
+// ------------------------------------------------------------ TMA producer
+// Streams one operand pair (A rows of `m_tile`, weight rows from `b_row`) for
+// `nkb` k-blocks into the smem ring.  Run by a whole warp; one elected lane
+// issues.  Everything that varies per k-block is kept as running coordinates
+// so the loop body is a wait, two TMA issues and three adds.
+//   full  : A is a full-width hidden buffer (panel layout; under tensor
+//           parallelism it arrives in per-rank chunks that are waited for).
+//   PAIR  : cta_group::2 — bytes are credited to the leader CTA's barrier.
+struct Ring { int stage; uint32_t phase; };
+template <bool PAIR, int STAGES, int STAGE_BYTES>
+__device__ __forceinline__ void produce_part(const CUtensorMap *map_a, const CUtensorMap *map_w,
+                                             int nkb, bool full, const uint32_t *wait,
+                                             uint32_t expect, int m_tile, int b_row,
+                                             const LayerArgs &args, uint8_t *smem,
+                                             uint64_t *full_bar, uint64_t *empty_bar, bool leader,
+                                             Ring &ring) {
+  if (nkb == 0) return;  // step 0: h == 0, no recurrent operand
+  const bool tp = full && args.tp_world > 1;
+  const int nchunks = tp ? args.tp_world : 1;
+  const int chunk_len = tp ? args.kb_rank : nkb;
+  const int pw = full ? (1 << args.pw_log2) : 0x7fffffff;
+  for (int c = 0; c < nchunks; ++c) {
+    // start with the chunk this rank produced itself, then walk the ring
+    int src = args.tp_rank + c;
+    if (src >= args.tp_world) src -= args.tp_world;
+    const int kb0 = tp ? src * args.kb_rank : 0;
+    bool fence = false;
+    if (tp && src != args.tp_rank) {
+      tp_wait_counter(wait + src * args.flag_stride + m_tile, expect);
+      fence = true;  // remote generic-proxy writes -> this chunk's TMA reads
+    }
+    int kw = kb0 * TC_BLOCK_K;
+    int ci = kw, co = m_tile * kTileM;
+    if (full) {
+      ci = kw & (pw - 1);
+      co += (kw >> args.pw_log2) * args.bpad;
+    }
+    for (int jj = 0; jj < chunk_len; ++jj) {
+      mbar_wait(&empty_bar[ring.stage], ring.phase ^ 1);
+      if (elect_one()) {
+        uint8_t *sa = smem + ring.stage * STAGE_BYTES;
+        uint8_t *sb = sa + TC_A_BYTES;
+        if (fence) fence_proxy_async();
+        if (PAIR) {
+          if (leader) mbar_expect_tx(&full_bar[ring.stage], 2 * STAGE_BYTES);
+          const uint32_t bar = mapa_u32(&full_bar[ring.stage], 0);
+          tma_load_2d_2sm(sa, map_a, bar, ci, co);
+          tma_load_2d_2sm(sb, map_w, bar, kw, b_row);
+        } else {
+          mbar_expect_tx(&full_bar[ring.stage], STAGE_BYTES);
+          tma_load_2d(sa, map_a, &full_bar[ring.stage], ci, co);
+          tma_load_2d(sb, map_w, &full_bar[ring.stage], kw, b_row);
+        }
+      }
+      __syncwarp();
+      fence = false;
+      if (++ring.stage == STAGES) { ring.stage = 0; ring.phase ^= 1; }
+      kw += TC_BLOCK_K;
+      ci += TC_BLOCK_K;
+      if (ci == pw) { ci = 0; co += args.bpad; }
     }
   }
 }
@@ -208,7 +299,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
                  const __grid_constant__ CUtensorMap map_h,
                  const __grid_constant__ CUtensorMap map_wx,
                  const __grid_constant__ CUtensorMap map_wh,
-                 const __grid_constant__ OutMaps outs, const LayerArgs args) {
+                 const __grid_constant__ CUtensorMap map_out, const LayerArgs args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -268,43 +359,16 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
 
   if (warp == 0) {
     // ===================================================== TMA producer
-    // The whole warp walks the loop (so everything stays warp-uniform and
-    // ptxas keeps descriptors in uniform registers); one elected lane issues.
-    int stage = 0;
-    uint32_t phase = 0;
+    Ring ring{0, 0};
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int m_tile = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
-      for (int kb = 0; kb < kb_total; ++kb) {
-        const bool is_x = kb < args.kb_x;
-        const int j = is_x ? kb : kb - args.kb_x;
-        int kblk = j;
-        bool tp_fence = false;
-        if (args.tp_world > 1 && (!is_x || args.x_full)) {
-          int src;
-          kblk = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
-          if (src != args.tp_rank && j % args.kb_rank == 0) {
-            // first k-block of a remote rank's chunk: acquire its counter once,
-            // then one proxy fence orders the TMA reads of the whole chunk
-            tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
-                            is_x ? args.expect_x : args.expect_h);
-            tp_fence = true;
-          }
-        }
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        if (elect_one()) {
-          uint8_t *sa = smem + stage * L_STAGE_BYTES;
-          uint8_t *sb = sa + TC_A_BYTES;
-          mbar_expect_tx(&full_bar[stage], TC_A_BYTES + L_B_BYTES);
-          if (tp_fence) fence_proxy_async();  // remote generic-proxy writes -> TMA reads
-          tma_load_2d(sa, is_x ? &map_x : &map_h, &full_bar[stage], kblk * TC_BLOCK_K,
-                      m_tile * kTileM);
-          tma_load_2d(sb, is_x ? &map_wx : &map_wh, &full_bar[stage], kblk * TC_BLOCK_K,
-                      n_blk * 192);
-        }
-        __syncwarp();
-        if (++stage == L_STAGES) { stage = 0; phase ^= 1; }
-      }
+      produce_part<false, L_STAGES, L_STAGE_BYTES>(&map_x, &map_wx, args.kb_x, args.x_full != 0,
+                                                   args.wait_x, args.expect_x, m_tile, n_blk * 192,
+                                                   args, smem, full_bar, empty_bar, true, ring);
+      produce_part<false, L_STAGES, L_STAGE_BYTES>(&map_h, &map_wh, args.kb_h, true, args.wait_h,
+                                                   args.expect_h, m_tile, n_blk * 192, args, smem,
+                                                   full_bar, empty_bar, true, ring);
     }
   } else if (warp == 1) {
     // ======================================================= MMA issuer
@@ -363,7 +427,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       const int row = m_tile * kTileM + r;
       const bool has_h = args.kb_h > 0;
       const int col = args.col0 + n_blk * 64;
-      const size_t hoff = (size_t)row * args.H + col + half * 32;
+      const size_t hoff = h_offset(row, col + half * 32, args.pw_log2, args.bpad);
       // previous hidden for this thread's 32 units: issue the loads before
       // waiting on the accumulator so their latency hides behind the MMAs
       uint4 hq[4];
@@ -378,9 +442,10 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
-      // the TMA stores that read this staging buffer two tiles ago are done
+      // the TMA store that read this staging buffer two tiles ago is done;
+      // publish the previous tile to the other tensor-parallel ranks
       if (issuer) tma_store_wait_read<1>();
-      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
+      epilogue_publish_prev(args, issuer, est, true);
 
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
@@ -389,10 +454,11 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);  // TMEM stage back to the MMAs
-      epilogue_store_tile(outs, args, stage_tile, col, m_tile, issuer, est);
+      epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, est);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
-    epilogue_finish(args, issuer, est);
+    if (issuer) tma_store_wait<0>();  // smem must outlive the store's reads
+    epilogue_publish_prev(args, issuer, est, true);
   }
 
   tc_fence_before();
@@ -423,7 +489,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
                       const __grid_constant__ CUtensorMap map_h,
                       const __grid_constant__ CUtensorMap map_wx,
                       const __grid_constant__ CUtensorMap map_wh,
-                      const __grid_constant__ OutMaps outs, const LayerArgs args) {
+                      const __grid_constant__ CUtensorMap map_out, const LayerArgs args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -486,43 +552,18 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
 
   if (warp == 0) {
     // ============================ TMA producer (both CTAs, own smem)
-    int stage = 0;
-    uint32_t phase = 0;
+    Ring ring{0, 0};
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       const int m2 = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
       const int m_tile = m2 * 2 + (int)rank;
-      for (int kb = 0; kb < kb_total; ++kb) {
-        const bool is_x = kb < args.kb_x;
-        const int j = is_x ? kb : kb - args.kb_x;
-        int kblk = j;
-        bool tp_fence = false;
-        if (args.tp_world > 1 && (!is_x || args.x_full)) {
-          int src;
-          kblk = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
-          if (src != args.tp_rank && j % args.kb_rank == 0) {
-            // first k-block of a remote rank's chunk: acquire its counter once,
-            // then one proxy fence orders the TMA reads of the whole chunk
-            tp_wait_counter((is_x ? args.wait_x : args.wait_h) + src * args.flag_stride + m_tile,
-                            is_x ? args.expect_x : args.expect_h);
-            tp_fence = true;
-          }
-        }
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        if (elect_one()) {
-          uint8_t *sa = smem + stage * P_STAGE_BYTES;
-          uint8_t *sb = sa + TC_A_BYTES;
-          // bytes of both CTAs land on the leader's barrier
-          if (leader) mbar_expect_tx(&full_bar[stage], 2 * P_STAGE_BYTES);
-          const uint32_t bar = mapa_u32(&full_bar[stage], 0);
-          if (tp_fence) fence_proxy_async();
-          tma_load_2d_2sm(sa, is_x ? &map_x : &map_h, bar, kblk * TC_BLOCK_K, m_tile * kTileM);
-          tma_load_2d_2sm(sb, is_x ? &map_wx : &map_wh, bar, kblk * TC_BLOCK_K,
-                          n_blk * 192 + (int)rank * 96);
-        }
-        __syncwarp();
-        if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
-      }
+      const int b_row = n_blk * 192 + (int)rank * 96;
+      produce_part<true, P_STAGES, P_STAGE_BYTES>(&map_x, &map_wx, args.kb_x, args.x_full != 0,
+                                                  args.wait_x, args.expect_x, m_tile, b_row, args,
+                                                  smem, full_bar, empty_bar, leader, ring);
+      produce_part<true, P_STAGES, P_STAGE_BYTES>(&map_h, &map_wh, args.kb_h, true, args.wait_h,
+                                                  args.expect_h, m_tile, b_row, args, smem,
+                                                  full_bar, empty_bar, leader, ring);
     }
   } else if (warp == 1) {
     // ========================================== MMA issuer (leader only)
@@ -582,7 +623,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       const int row = m_tile * kTileM + r;
       const bool has_h = args.kb_h > 0;
       const int col = args.col0 + n_blk * 64;
-      const size_t hoff = (size_t)row * args.H + col + half * 32;
+      const size_t hoff = h_offset(row, col + half * 32, args.pw_log2, args.bpad);
       uint4 hq[4];
       if (has_h) {
         const uint4 *src = reinterpret_cast<const uint4 *>(args.h_prev + hoff);
@@ -596,7 +637,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
       if (issuer) tma_store_wait_read<1>();
-      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
+      epilogue_publish_prev(args, issuer, est, true);
 
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
@@ -605,10 +646,11 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
-      epilogue_store_tile(outs, args, stage_tile, col, m_tile, issuer, est);
+      epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, est);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
-    epilogue_finish(args, issuer, est);
+    if (issuer) tma_store_wait<0>();  // smem must outlive the store's reads
+    epilogue_publish_prev(args, issuer, est, true);
   }
 
   tc_fence_before();
@@ -639,6 +681,7 @@ struct FcArgs {
   int tp_world, tp_rank, kb_rank, flag_stride;
   uint32_t expect_h;
   const uint32_t *wait_h;
+  int pw_log2, bpad;        // panel layout of the hidden buffer
 };
 
 __global__ void __launch_bounds__(F_THREADS, 1)
@@ -685,7 +728,9 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t *sa = smem + stage * F_STAGE_BYTES;
           mbar_expect_tx(&full_bar[stage], TC_A_BYTES + b_bytes);
-          tma_load_2d(sa, &map_h, &full_bar[stage], kb * TC_BLOCK_K, tile * kTileM);
+          int ci, co;
+          h_coords(tile * kTileM, kb * TC_BLOCK_K, args.pw_log2, args.bpad, &ci, &co);
+          tma_load_2d(sa, &map_h, &full_bar[stage], ci, co);
           tma_load_2d(sa + TC_A_BYTES, &map_w, &full_bar[stage], kb * TC_BLOCK_K, 0);
           if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
         }
@@ -807,7 +852,7 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
 // with the gate order of the packed block given by (g0,g1,g2).
 __global__ void pack_gate_weights_kernel(const float *__restrict__ src,
                                          __nv_bfloat16 *__restrict__ dst, int H,
-                                         int Hs, int unit0, int K, int g0, int g1, int g2) {
+                                         int Hs, int unit0, int K, int ld, int g0, int g1, int g2) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   size_t total = (size_t)3 * Hs * K;
   if (idx >= total) return;
@@ -816,13 +861,13 @@ __global__ void pack_gate_weights_kernel(const float *__restrict__ src,
   int jb = (int)(prow / 192), rem = (int)(prow % 192);
   int slot = rem / 64, u = rem % 64;
   int g = slot == 0 ? g0 : (slot == 1 ? g1 : g2);
-  dst[idx] = __float2bfloat16_rn(src[((size_t)g * H + unit0 + jb * 64 + u) * K + k]);
+  dst[prow * ld + k] = __float2bfloat16_rn(src[((size_t)g * H + unit0 + jb * 64 + u) * K + k]);
 }
 
 __global__ void to_bf16_kernel(const float *__restrict__ src,
-                               __nv_bfloat16 *__restrict__ dst, size_t n) {
+                               __nv_bfloat16 *__restrict__ dst, size_t n, int cols, int ld) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx < n) dst[idx] = __float2bfloat16_rn(src[idx]);
+  if (idx < n) dst[(idx / cols) * ld + idx % cols] = __float2bfloat16_rn(src[idx]);
 }
 
 // Layer-0 "x weights": t0w[jb][slot][u][c], slots (n, r, z), K = kx >= C:
@@ -937,8 +982,9 @@ size_t tp_shared_bytes(const b200gru_model *m) {
 static int make_h_maps(b200gru_model *m) {
   for (int l = 0; l < m->cfg.num_layers; ++l)
     for (int pp = 0; pp < 2; ++pp)
-      if (int rc = make_tmap_bf16_2d(&m->tc[l].map_h[pp], m->tc[l].h[pp], (uint64_t)m->bpad,
-                                     (uint64_t)m->cfg.hidden, kTileM, 64))
+      if (int rc = make_tmap_bf16_2d(&m->tc[l].map_h[pp], m->tc[l].h[pp],
+                                     (uint64_t)m->bpad * (m->cfg.hidden >> m->pw_log2),
+                                     (uint64_t)1 << m->pw_log2, kTileM, 64))
         return rc;
   return 0;
 }
@@ -963,13 +1009,6 @@ int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
   for (int l = 0; l < L; ++l)
     for (int pp = 0; pp < 2; ++pp) m->tc[l].h[pp] = m->tp_h[m->tp_rank][l][pp];
   if (int rc = make_h_maps(m)) return rc;
-  // store maps over every rank's copy of every hidden buffer (peer addresses)
-  for (int r = 0; r < m->tp_world; ++r)
-    for (int l = 0; l < L; ++l)
-      for (int pp = 0; pp < 2; ++pp)
-        if (int rc = make_tmap_bf16_2d(&m->tp_map_h[r][l][pp], m->tp_h[r][l][pp], (uint64_t)m->bpad,
-                                       (uint64_t)m->cfg.hidden, kTileM, 64))
-          return rc;
   m->tp_bound = true;
   return 0;
 }
@@ -983,6 +1022,16 @@ int tc_prepare(b200gru_model *m) {
   auto blocks = [&](size_t n) { return (unsigned)((n + TPB - 1) / TPB); };
   const int kx = (C + 63) / 64 * 64;
   m->kx = kx;
+  const int ld = m->ldh;
+  {
+    // panel width of the hidden buffers: row-major unless tensor parallel, where
+    // peers write 128-byte row segments over NVLink (B200GRU_PANEL overrides)
+    int pw = m->tp_world > 1 ? 64 : H;
+    if (const char *e = getenv("B200GRU_PANEL")) pw = atoi(e);
+    if (pw < 64 || pw > H || (pw & (pw - 1)) || H % pw) pw = (H & (H - 1)) ? 64 : H;
+    m->pw_log2 = 0;
+    while ((1 << m->pw_log2) < pw) ++m->pw_log2;
+  }
 
   // layer-0 input: one-hot rows and the T0 table as a K-major weight
   if (int rc = tc_alloc(m, &m->onehot, (size_t)m->bpad * kx)) return rc;
@@ -997,35 +1046,39 @@ int tc_prepare(b200gru_model *m) {
 
   for (int l = 0; l < L; ++l) {
     TcLayer &t = m->tc[l];
-    const size_t wn = (size_t)3 * Hs * H;
+    const size_t wn = (size_t)3 * Hs * ld;   // padded rows
+    const size_t we = (size_t)3 * Hs * H;    // elements to convert
     if (l > 0) {
       if (int rc = tc_alloc(m, &t.w_ih, wn)) return rc;
       // x-part column order [n_i | r | z]
-      pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_i(l, 0)), t.w_ih, H, Hs, unit0, H,
+      B200_CUDA(cudaMemset(t.w_ih, 0, wn * sizeof(__nv_bfloat16)));
+      pack_gate_weights_kernel<<<blocks(we), TPB>>>(m->P(ix.w_i(l, 0)), t.w_ih, H, Hs, unit0, H, ld,
                                                     2, 0, 1);
-      if (int rc = make_tmap_bf16_2d(&t.map_w_ih, t.w_ih, 3 * (uint64_t)Hs, H, 192, 64)) return rc;
-      if (int rc = make_tmap_bf16_2d(&t.map_w_ih_p, t.w_ih, 3 * (uint64_t)Hs, H, 96, 64)) return rc;
+      if (int rc = make_tmap_bf16_2d(&t.map_w_ih, t.w_ih, 3 * (uint64_t)Hs, H, 192, 64, ld)) return rc;
+      if (int rc = make_tmap_bf16_2d(&t.map_w_ih_p, t.w_ih, 3 * (uint64_t)Hs, H, 96, 64, ld)) return rc;
     }
     if (int rc = tc_alloc(m, &t.w_hh, wn)) return rc;
     // h-part column order [r | z | n_h]
-    pack_gate_weights_kernel<<<blocks(wn), TPB>>>(m->P(ix.w_h(l, 0)), t.w_hh, H, Hs, unit0, H,
+    B200_CUDA(cudaMemset(t.w_hh, 0, wn * sizeof(__nv_bfloat16)));
+    pack_gate_weights_kernel<<<blocks(we), TPB>>>(m->P(ix.w_h(l, 0)), t.w_hh, H, Hs, unit0, H, ld,
                                                   0, 1, 2);
-    if (int rc = make_tmap_bf16_2d(&t.map_w_hh, t.w_hh, 3 * (uint64_t)Hs, H, 192, 64)) return rc;
-    if (int rc = make_tmap_bf16_2d(&t.map_w_hh_p, t.w_hh, 3 * (uint64_t)Hs, H, 96, 64)) return rc;
+    if (int rc = make_tmap_bf16_2d(&t.map_w_hh, t.w_hh, 3 * (uint64_t)Hs, H, 192, 64, ld)) return rc;
+    if (int rc = make_tmap_bf16_2d(&t.map_w_hh_p, t.w_hh, 3 * (uint64_t)Hs, H, 96, 64, ld)) return rc;
     if (int rc = tc_alloc(m, &t.bias, (size_t)4 * Hs)) return rc;
     pack_bias_kernel<<<blocks((size_t)4 * Hs), TPB>>>(m->P(ix.b_i(l, 0)), m->P(ix.b_h(l, 0)),
                                                       t.bias, H, Hs, unit0, l == 0 ? 1 : 0);
-    if (m->tp_world == 1)
+    if (m->tp_world == 1 || m->tp_fake)
       for (int pp = 0; pp < 2; ++pp) {
         if (int rc = tc_alloc(m, &t.h[pp], (size_t)m->bpad * H)) return rc;
         B200_CUDA(cudaMemset(t.h[pp], 0, sizeof(__nv_bfloat16) * (size_t)m->bpad * H));
       }
   }
-  if (m->tp_world == 1)
+  if (m->tp_world == 1 || m->tp_fake)
     if (int rc = make_h_maps(m)) return rc;
-  if (int rc = tc_alloc(m, &m->w_fc, (size_t)C * H)) return rc;
-  to_bf16_kernel<<<blocks((size_t)C * H), TPB>>>(m->P(ix.w_fc()), m->w_fc, (size_t)C * H);
-  if (int rc = make_tmap_bf16_2d(&m->map_w_fc, m->w_fc, (uint64_t)C, H, C, 64)) return rc;
+  if (int rc = tc_alloc(m, &m->w_fc, (size_t)C * ld)) return rc;
+  B200_CUDA(cudaMemset(m->w_fc, 0, sizeof(__nv_bfloat16) * (size_t)C * ld));
+  to_bf16_kernel<<<blocks((size_t)C * H), TPB>>>(m->P(ix.w_fc()), m->w_fc, (size_t)C * H, H, ld);
+  if (int rc = make_tmap_bf16_2d(&m->map_w_fc, m->w_fc, (uint64_t)C, H, C, 64, ld)) return rc;
   B200_CUDA(cudaGetLastError());
 
   B200_CUDA(cudaFuncSetAttribute(gru_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1053,8 +1106,10 @@ static int num_sms(int device) {
 int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
   const b200gru_config &c = m->cfg;
   const int H = c.hidden, C = c.num_char, T = c.max_len, L = c.num_layers;
-  const int W = m->tp_world, R = m->tp_rank;
-  const int Hs = H / W;
+  // tp_fake: profile ONE rank's share of a tensor-parallel model on a single GPU
+  // (sliced shapes, no peers, no waits; the numbers it samples are meaningless)
+  const int W = m->tp_fake ? 1 : m->tp_world, R = m->tp_rank;
+  const int Hs = H / m->tp_world;
   const int sms = num_sms(m->device);
   int launches = 0;
   const int m_tiles = (n + kTileM - 1) / kTileM;
@@ -1084,17 +1139,14 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
       a.n = n; a.m_tiles = m_tiles; a.n_blocks = Hs / kUnitBlock;
       a.kb_x = (l == 0 ? m->kx : H) / TC_BLOCK_K;
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
-      a.H = H; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
+      a.pw_log2 = m->pw_log2; a.bpad = m->bpad; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
       a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.x_full = l > 0;
       a.col0 = R * Hs; a.flag_stride = mt_max;
       a.h_out_peer[0] = t.h[wr];
-      OutMaps outs;
-      outs.m[0] = t.map_h[wr];
       if (W > 1) {
         m->tp_rounds[l][wr] += 1;  // this launch is one more write round of buffer (l, wr)
         for (int r = 0; r < W; ++r) {
           a.h_out_peer[r] = m->tp_h[r][l][wr];
-          outs.m[r] = m->tp_map_h[r][l][wr];
           a.signal_peer[r] = m->tp_cnt[r][l][wr] + (size_t)R * mt_max;
         }
         a.wait_h = m->tp_cnt[R][l][rd];
@@ -1123,12 +1175,12 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
         cfg.numAttrs = 1;
         B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_pair_kernel,
                                      l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-                                     l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p, outs, a));
+                                     l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p, t.map_h[wr], a));
       } else {
         const int grid = tiles < sms ? tiles : sms;
         gru_layer_kernel<<<grid, L_THREADS, L_SMEM_BYTES, s>>>(
             l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-            l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, outs, a);
+            l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, t.map_h[wr], a);
       }
       ++launches;
       m->trace_mark(l == 0 ? "layer0" : "layerN", s);
@@ -1140,6 +1192,7 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
     a.rfloats = io->rfloats; a.output = io->output;
     a.chars = m->chars; a.alive = m->alive; a.onehot = m->onehot;
     a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.flag_stride = mt_max;
+    a.pw_log2 = m->pw_log2; a.bpad = m->bpad;
     if (W > 1) {
       a.wait_h = m->tp_cnt[R][L - 1][wr];
       a.expect_h = m->tp_rounds[L - 1][wr] * per_round;

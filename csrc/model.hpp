@@ -54,6 +54,9 @@ struct b200gru_model {
   int32_t *chars = nullptr; // [bpad]
   uint8_t *alive = nullptr; // [bpad]
   // --- tensor-core path
+  int ldh = 0;                       // row stride (elements) of hidden buffers and K=H weights
+                                     // (H + B200GRU_LD_PAD; padding measured: no effect, default 0)
+  int pw_log2 = 0;                   // hidden buffers: [H/pw panels][bpad][pw], pw = 1 << pw_log2
   int kx = 0;                        // one-hot row length: num_char rounded up to 64
   __nv_bfloat16 *onehot = nullptr;   // [bpad, kx]  layer-0 x operand
   __nv_bfloat16 *t0w = nullptr;      // [H/64][192][kx] layer-0 table as K-major weights
@@ -68,10 +71,10 @@ struct b200gru_model {
   // --- tensor parallelism over the hidden dimension (tp_world == 1: off)
   int tp_world = 1, tp_rank = 0;
   bool tp_bound = false;
+  bool tp_fake = false;   // B200GRU_TP_FAKE=1: single-GPU profiling of one rank's shapes
   uint32_t tp_epoch = 0;                                   // completed generate calls
   uint32_t tp_rounds[B200GRU_MAX_LAYERS][2] = {};          // write rounds per hidden buffer
   __nv_bfloat16 *tp_h[8][B200GRU_MAX_LAYERS][2] = {};      // [rank][layer][pp] hidden buffers
-  CUtensorMap tp_map_h[8][B200GRU_MAX_LAYERS][2];          // TMA store maps over tp_h
   uint32_t *tp_cnt[8][B200GRU_MAX_LAYERS][2] = {};         // [rank][layer][pp] -> [src][m_tile]
   uint32_t *tp_sync[8] = {};                               // [rank] -> [src] call-fence words
 
@@ -117,5 +120,6 @@ size_t tp_shared_bytes(const b200gru_model *m);
 int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases);
 // TMA descriptor helper (tma_host.cu)
 int make_tmap_bf16_2d(CUtensorMap *map, const void *base, uint64_t rows,
-                      uint64_t cols, uint32_t box_rows, uint32_t box_cols);
+                      uint64_t cols, uint32_t box_rows, uint32_t box_cols,
+                      uint64_t ld = 0);
 }  // namespace b200gru

@@ -96,3 +96,34 @@ int b200gru_can_access_peer(int device, int peer) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------ diagnostics
+// Store `rows` rows of `row_bytes` bytes (row pitch `pitch`) to up to 8
+// destination buffers (typically peer-mapped) from `src`, with 16-byte
+// stores, every warp covering contiguous bytes of a row.  Used by
+// tools/p2p_bench.py to measure NVLink write bandwidth for the access pattern
+// the tensor-parallel epilogue produces.
+struct P2PDst { unsigned char *p[8]; };
+__global__ void p2p_write_kernel(P2PDst dst, int ndst, const unsigned char *src, long long rows,
+                                 int row_bytes, long long pitch) {
+  const int chunks_per_row = row_bytes / 16;
+  const long long total = rows * chunks_per_row;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / chunks_per_row;
+    const int c = (int)(i % chunks_per_row);
+    const uint4 v = *reinterpret_cast<const uint4 *>(src + r * pitch + c * 16);
+    for (int d = 0; d < ndst; ++d) *reinterpret_cast<uint4 *>(dst.p[d] + r * pitch + c * 16) = v;
+  }
+}
+
+extern "C" int b200gru_p2p_write_bench(void *const *dsts, int ndst, const void *src, long long rows,
+                                       int row_bytes, long long pitch, int blocks, void *stream) {
+  B200_REQUIRE(dsts && src && ndst >= 1 && ndst <= 8 && row_bytes % 16 == 0, "bad arguments");
+  P2PDst d{};
+  for (int i = 0; i < ndst; ++i) d.p[i] = static_cast<unsigned char *>(dsts[i]);
+  p2p_write_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      d, ndst, static_cast<const unsigned char *>(src), rows, row_bytes, pitch);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}

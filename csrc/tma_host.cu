@@ -22,18 +22,20 @@ static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
 
 // Row-major bf16 matrix [rows, cols]; box = box_rows x box_cols elements with
 // the 128-byte swizzle the UMMA descriptors in sm100_ptx.cuh expect
-// (box_cols * 2 bytes must be 128).
+// (box_cols * 2 bytes must be 128).  `ld` = row stride in elements (0: dense).
 int make_tmap_bf16_2d(CUtensorMap *map, const void *base, uint64_t rows,
-                      uint64_t cols, uint32_t box_rows, uint32_t box_cols) {
+                      uint64_t cols, uint32_t box_rows, uint32_t box_cols,
+                      uint64_t ld) {
+  if (ld == 0) ld = cols;
   auto fn = encode_fn();
   if (!fn) return fail(B200GRU_ERR_CUDA, "cuTensorMapEncodeTiled unavailable");
   B200_REQUIRE(box_cols * 2 == 128, "box inner extent must be 128 bytes");
   B200_REQUIRE(box_rows >= 1 && box_rows <= 256, "box rows %u", box_rows);
   B200_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 &&
-                   (cols * 2) % 16 == 0,
+                   (ld * 2) % 16 == 0 && ld >= cols,
                "tensor map base/stride must be 16-byte aligned");
   cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstride[1] = {cols * 2};
+  cuuint64_t gstride[1] = {ld * 2};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,

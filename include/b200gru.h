@@ -189,6 +189,13 @@ int b200gru_memset_async(void *dst, int value, size_t bytes, void *stream);
 int b200gru_signal_flag(uint32_t *flag, uint32_t value, void *stream);
 int b200gru_can_access_peer(int device, int peer);
 
+/* Diagnostic: write `rows` x `row_bytes` (row pitch `pitch`) from `src` to
+ * `ndst` destination buffers with coalesced 16-byte stores; tools/p2p_bench.py
+ * times it to measure NVLink write bandwidth per access pattern. */
+int b200gru_p2p_write_bench(void *const *dsts, int ndst, const void *src,
+                            long long rows, int row_bytes, long long pitch,
+                            int blocks, void *stream);
+
 /* ------------------------------------------------- stand-alone device ops */
 /* D[M,N] (fp32) = A[M,K] (bf16, row-major) x B[N,K]^T (bf16, row-major) on
  * tcgen05; used by tests to validate descriptors / TMA / TMEM plumbing. */
