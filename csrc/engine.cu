@@ -136,6 +136,10 @@ int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
   m->tp_rank = tp_rank;
   m->tp_world = tp_world;
   {
+    const char *e = getenv("B200GRU_GRAPH");
+    m->use_graph = !(e && e[0] == '0');
+  }
+  {
     const char *e = getenv("B200GRU_TP_FAKE");
     m->tp_fake = tp_world > 1 && e && e[0] == '1';
   }
@@ -164,6 +168,8 @@ int b200gru_model_destroy(b200gru_model *m) {
   DeviceGuard guard(m->device);
   cudaError_t first = cudaDeviceSynchronize();
   for (cudaEvent_t e : m->trace_ev) cudaEventDestroy(e);
+  for (auto &g : m->graphs) cudaGraphExecDestroy(g.exec);
+  if (m->cap_stream) cudaStreamDestroy(m->cap_stream);
   for (void *p : m->allocs) {
     cudaError_t e = cudaFree(p);
     if (first == cudaSuccess) first = e;
@@ -199,7 +205,57 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
                   "tensor-core mode needs hidden %% 64 == 0 and num_char a "
                   "multiple of 16 in [16,256] (got H=%d, C=%d)",
                   m->cfg.hidden, m->cfg.num_char);
-    return tc_generate(m, n, io, s);
+    // Replay a captured graph when nothing about the call varies: no
+    // completion flag (its value changes per call), no tensor-parallel
+    // counters, no tracing.
+    const bool graphable = m->use_graph && m->tp_world == 1 && !io->done_flag && !m->trace_on;
+    if (!graphable) return tc_generate(m, n, io, s);
+    for (auto &g : m->graphs)
+      if (g.n == n && g.rfloats == io->rfloats && g.output == io->output &&
+          g.logits == m->debug_logits) {
+        g.last_use = ++m->graph_clock;
+        m->last_launches = g.launches;
+        B200_CUDA(cudaGraphLaunch(g.exec, s));
+        return 0;
+      }
+    // Capture on a private stream (the caller's may be the legacy default
+    // stream, which cannot be captured); the graph is launched on the caller's.
+    if (!m->cap_stream)
+      B200_CUDA(cudaStreamCreateWithFlags(&m->cap_stream, cudaStreamNonBlocking));
+    cudaGraph_t graph = nullptr;
+    B200_CUDA(cudaStreamBeginCapture(m->cap_stream, cudaStreamCaptureModeThreadLocal));
+    int rc = tc_generate(m, n, io, m->cap_stream);
+    cudaError_t ce = cudaStreamEndCapture(m->cap_stream, &graph);
+    if (rc) {
+      if (graph) cudaGraphDestroy(graph);
+      return rc;
+    }
+    if (ce != cudaSuccess || !graph) {  // capture not possible here: run eagerly
+      cudaGetLastError();
+      m->use_graph = false;
+      return tc_generate(m, n, io, s);
+    }
+    b200gru_model::GraphEntry e;
+    ce = cudaGraphInstantiate(&e.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ce != cudaSuccess) {
+      cudaGetLastError();
+      m->use_graph = false;
+      return tc_generate(m, n, io, s);
+    }
+    e.n = n; e.rfloats = io->rfloats; e.output = io->output; e.logits = m->debug_logits;
+    e.launches = m->last_launches; e.last_use = ++m->graph_clock;
+    if (m->graphs.size() >= 8) {  // evict the least recently used
+      size_t victim = 0;
+      for (size_t i = 1; i < m->graphs.size(); ++i)
+        if (m->graphs[i].last_use < m->graphs[victim].last_use) victim = i;
+      cudaGraphExecDestroy(m->graphs[victim].exec);
+      m->graphs[victim] = e;
+    } else {
+      m->graphs.push_back(e);
+    }
+    B200_CUDA(cudaGraphLaunch(e.exec, s));
+    return 0;
   }
   return fail(B200GRU_ERR_ARG, "unknown mode %d", mode);
 }

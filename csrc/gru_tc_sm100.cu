@@ -107,15 +107,6 @@ __device__ __forceinline__ void h_coords(int row, int col, int pw_log2, int bpad
   *co = panel * bpad + row;
 }
 
-// K-block order under tensor parallelism: start with the chunk this rank
-// produced itself, then walk the ring, so remote chunks have time to land.
-__device__ __forceinline__ int tp_kblock(int j, int kb_rank, int world, int rank, int *src) {
-  const int c = j / kb_rank;
-  int q = rank + c;
-  if (q >= world) q -= world;
-  *src = q;
-  return q * kb_rank + (j - c * kb_rank);
-}
 // All lanes poll (one coalesced request); every lane has then acquired.
 __device__ __forceinline__ void tp_wait_counter(const uint32_t *p, uint32_t expect) {
   while ((int32_t)(ld_acquire_sys(p) - expect) < 0) __nanosleep(64);
@@ -711,53 +702,69 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x)
-        for (int j = 0; j < args.kb; ++j) {
-          int kb = j;
-          if (args.tp_world > 1) {
-            int src;
-            kb = tp_kblock(j, args.kb_rank, args.tp_world, args.tp_rank, &src);
-            if (src != args.tp_rank && j % args.kb_rank == 0) {
-              tp_wait_counter(args.wait_h + src * args.flag_stride + tile, args.expect_h);
-              fence_proxy_async();
-            }
-          }
+    // TMA producer: warp-converged, one elected lane issues (see produce_part)
+    int stage = 0;
+    uint32_t phase = 0;
+    const bool tp = args.tp_world > 1;
+    const int nchunks = tp ? args.tp_world : 1;
+    const int chunk_len = tp ? args.kb_rank : args.kb;
+    const int pw = 1 << args.pw_log2;
+    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x)
+      for (int c = 0; c < nchunks; ++c) {
+        int src = args.tp_rank + c;
+        if (src >= args.tp_world) src -= args.tp_world;
+        bool fence = false;
+        if (tp && src != args.tp_rank) {
+          tp_wait_counter(args.wait_h + src * args.flag_stride + tile, args.expect_h);
+          fence = true;
+        }
+        int kw = tp ? src * args.kb_rank * TC_BLOCK_K : 0;
+        int ci = kw & (pw - 1);
+        int co = tile * kTileM + (kw >> args.pw_log2) * args.bpad;
+        for (int jj = 0; jj < chunk_len; ++jj) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t *sa = smem + stage * F_STAGE_BYTES;
-          mbar_expect_tx(&full_bar[stage], TC_A_BYTES + b_bytes);
-          int ci, co;
-          h_coords(tile * kTileM, kb * TC_BLOCK_K, args.pw_log2, args.bpad, &ci, &co);
-          tma_load_2d(sa, &map_h, &full_bar[stage], ci, co);
-          tma_load_2d(sa + TC_A_BYTES, &map_w, &full_bar[stage], kb * TC_BLOCK_K, 0);
+          if (elect_one()) {
+            uint8_t *sa = smem + stage * F_STAGE_BYTES;
+            if (fence) fence_proxy_async();
+            mbar_expect_tx(&full_bar[stage], TC_A_BYTES + b_bytes);
+            tma_load_2d(sa, &map_h, &full_bar[stage], ci, co);
+            tma_load_2d(sa + TC_A_BYTES, &map_w, &full_bar[stage], kw, 0);
+          }
+          __syncwarp();
+          fence = false;
           if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
+          kw += TC_BLOCK_K;
+          ci += TC_BLOCK_K;
+          if (ci == pw) { ci = 0; co += args.bpad; }
         }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      int stage = 0, acc_stage = 0;
-      uint32_t phase = 0, acc_phase = 0;
-      const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)C);
-      for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x) {
-        mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
-        for (int kb = 0; kb < args.kb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * F_STAGE_BYTES);
-          const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + TC_A_BYTES);
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_bf16(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(&empty_bar[stage]);
-          if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
-        }
-        umma_commit(&tmem_full[acc_stage]);
-        if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
       }
+  } else if (warp == 1) {
+    // MMA issuer: warp-converged, elected lane issues four UMMAs per k-block
+    int stage = 0, acc_stage = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)C);
+    const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
+    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x) {
+      mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
+      for (int kb = 0; kb < args.kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint64_t da = desc0 + (uint64_t)((stage * F_STAGE_BYTES) >> 4);
+          const uint64_t db = da + (uint64_t)(TC_A_BYTES >> 4);
+          umma_bf16(d, da, db, idesc, kb != 0 ? 1u : 0u);
+          umma_bf16(d, da + 2, db + 2, idesc, 1u);
+          umma_bf16(d, da + 4, db + 4, idesc, 1u);
+          umma_bf16(d, da + 6, db + 6, idesc, 1u);
+          umma_commit(&empty_bar[stage]);
+          if (kb == args.kb - 1) umma_commit(&tmem_full[acc_stage]);
+        }
+        __syncwarp();
+        if (++stage == F_STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
   } else if (warp >= 4) {
     const int quarter = warp & 3;

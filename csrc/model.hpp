@@ -78,6 +78,23 @@ struct b200gru_model {
   uint32_t *tp_cnt[8][B200GRU_MAX_LAYERS][2] = {};         // [rank][layer][pp] -> [src][m_tile]
   uint32_t *tp_sync[8] = {};                               // [rank] -> [src] call-fence words
 
+  // --- CUDA graphs: the 31 launches of a tensor-core generate are captured once
+  // per (n, io) and replayed, which removes the per-launch CPU cost that
+  // dominates small batches (B200GRU_GRAPH=0 disables)
+  struct GraphEntry {
+    int n = 0;
+    const void *rfloats = nullptr;
+    void *output = nullptr;
+    bool logits = false;
+    cudaGraphExec_t exec = nullptr;
+    int launches = 0;
+    uint64_t last_use = 0;
+  };
+  std::vector<GraphEntry> graphs;
+  uint64_t graph_clock = 0;
+  bool use_graph = true;
+  cudaStream_t cap_stream = nullptr;
+
   // --- tracing: CUDA events between launches (the reference has no timers at all)
   bool trace_on = false;
   std::vector<cudaEvent_t> trace_ev;
