@@ -65,7 +65,7 @@ class DPContext:
         if n_names > self.max_total:
             raise ValueError(f"n_names={n_names} > max_names_total={self.max_total}")
         if self.method == "nccl":
-            return self._generate_nccl(gen, n_names, random_floats, mode)
+            return self._generate_nccl(gen, n_names, random_floats, mode, to_host)
         cfg = self.cfg
         T = cfg.max_len
         sl = partition(n_names, self.world, self.rank, self.drop_remainder)
@@ -116,23 +116,29 @@ class DPContext:
         gen.last_launches = launches
         return result
 
-    def _generate_nccl(self, gen, n_names, random_floats, mode):
+    def _generate_nccl(self, gen, n_names, random_floats, mode, to_host=True):
+        """Baseline: the reference's structure with NCCL in place of MPI —
+        scatter (:636), local generate, gather (:889)."""
         cfg = self.cfg
         T = cfg.max_len
         sl = partition(n_names, self.world, self.rank, True)
         dev = torch.device("cuda", self.device)
-        mine = torch.empty(sl.jpp * T, dtype=torch.float32, device=dev)
+        if getattr(self, "_mine", None) is None or self._mine.numel() != sl.jpp * T:
+            self._mine = torch.empty(sl.jpp * T, dtype=torch.float32, device=dev)
         if self.rank == 0:
-            full = random_floats.reshape(-1)[: sl.jpp * self.world * T].to(dev, non_blocking=True)
-            chunks = list(full.view(self.world, sl.jpp * T).unbind(0))
+            if random_floats is not None:  # None: reuse the floats already on the device
+                self._full = random_floats.reshape(-1)[: sl.jpp * self.world * T].to(dev, non_blocking=True)
+            chunks = list(self._full.view(self.world, sl.jpp * T).unbind(0))
         else:
             chunks = None
-        dist.scatter(mine, chunks, src=0, group=self.group)
-        out = gen.generate_device(mine, sl.jpp, mode=mode).contiguous()
+        dist.scatter(self._mine, chunks, src=0, group=self.group)
+        out = gen.generate_device(self._mine, sl.jpp, mode=mode).contiguous()
         gathered = [torch.empty_like(out) for _ in range(self.world)] if self.rank == 0 else None
         dist.gather(out, gathered, dst=0, group=self.group)
-        if self.rank != 0:
-            torch.cuda.current_stream(self.device).synchronize()
+        gen.last_launches += 2
+        if self.rank != 0 or not to_host:
+            if to_host:
+                torch.cuda.current_stream(self.device).synchronize()
             return None
         res = torch.zeros(n_names, T + 1, dtype=torch.uint8)
         res[: sl.jpp * self.world] = torch.cat(gathered, 0).cpu()
