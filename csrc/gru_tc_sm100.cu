@@ -347,6 +347,11 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  // Everything above touched only this CTA's smem / TMEM; it may overlap the
+  // tail of the previous kernel (programmatic dependent launch).  From here on
+  // global data written by earlier kernels is read.
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     // ===================================================== TMA producer
@@ -540,6 +545,8 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
   tc_fence_before();
   cluster_sync_all();  // both CTAs allocated + zeroed before the leader's MMAs
   tc_fence_after();
+  pdl_launch_dependents();
+  pdl_wait();  // see gru_layer_kernel
 
   if (warp == 0) {
     // ============================ TMA producer (both CTAs, own smem)
@@ -700,6 +707,8 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();  // prologue above may overlap the previous kernel's tail
 
   if (warp == 0) {
     // TMA producer: warp-converged, one elected lane issues (see produce_part)
@@ -1095,6 +1104,8 @@ int tc_prepare(b200gru_model *m) {
   {
     const char *e = getenv("B200GRU_CTA_PAIRS");
     m->use_pairs = !(e && e[0] == '0');
+    e = getenv("B200GRU_PDL");
+    m->use_pdl = !(e && e[0] == '0');
   }
   B200_CUDA(cudaFuncSetAttribute(fc_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  F_SMEM_BYTES));
@@ -1164,30 +1175,44 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
         }
       }
       const int tiles = a.m_tiles * a.n_blocks;
-      if (m->use_pairs && m_tiles >= 2) {
-        // 256-name tiles on CTA pairs (clusters of 2, one pair per TPC)
-        const int tiles2 = ((m_tiles + 1) / 2) * a.n_blocks;
-        const int pairs = tiles2 < sms / 2 ? tiles2 : sms / 2;
+      {
+        const bool pairs = m->use_pairs && m_tiles >= 2;
         cudaLaunchConfig_t cfg{};
-        cfg.gridDim = dim3(2 * pairs);
+        cudaLaunchAttribute attr[2];
+        int na = 0;
+        if (m->use_pdl) {  // prologue overlaps the previous kernel's tail
+          attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+          attr[na].val.programmaticStreamSerializationAllowed = 1;
+          ++na;
+        }
         cfg.blockDim = dim3(L_THREADS);
-        cfg.dynamicSmemBytes = P_SMEM_BYTES;
         cfg.stream = s;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_pair_kernel,
-                                     l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-                                     l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p, t.map_h[wr], a));
-      } else {
-        const int grid = tiles < sms ? tiles : sms;
-        gru_layer_kernel<<<grid, L_THREADS, L_SMEM_BYTES, s>>>(
-            l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-            l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, t.map_h[wr], a);
+        if (pairs) {
+          // 256-name tiles on CTA pairs (clusters of 2, one pair per TPC)
+          const int tiles2 = ((m_tiles + 1) / 2) * a.n_blocks;
+          const int npairs = tiles2 < sms / 2 ? tiles2 : sms / 2;
+          cfg.gridDim = dim3(2 * npairs);
+          cfg.dynamicSmemBytes = P_SMEM_BYTES;
+          attr[na].id = cudaLaunchAttributeClusterDimension;
+          attr[na].val.clusterDim.x = 2;
+          attr[na].val.clusterDim.y = 1;
+          attr[na].val.clusterDim.z = 1;
+          ++na;
+          cfg.attrs = attr;
+          cfg.numAttrs = na;
+          B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_pair_kernel,
+                                       l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
+                                       l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p,
+                                       t.map_h[wr], a));
+        } else {
+          cfg.gridDim = dim3(tiles < sms ? tiles : sms);
+          cfg.dynamicSmemBytes = L_SMEM_BYTES;
+          cfg.attrs = attr;
+          cfg.numAttrs = na;
+          B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_kernel,
+                                       l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
+                                       l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, t.map_h[wr], a));
+        }
       }
       ++launches;
       m->trace_mark(l == 0 ? "layer0" : "layerN", s);
@@ -1204,8 +1229,19 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
       a.wait_h = m->tp_cnt[R][L - 1][wr];
       a.expect_h = m->tp_rounds[L - 1][wr] * per_round;
     }
-    const int grid = m_tiles < sms ? m_tiles : sms;
-    fc_sample_kernel<<<grid, F_THREADS, F_SMEM_BYTES, s>>>(m->tc[L - 1].map_h[wr], m->map_w_fc, a);
+    {
+      cudaLaunchConfig_t cfg{};
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.gridDim = dim3(m_tiles < sms ? m_tiles : sms);
+      cfg.blockDim = dim3(F_THREADS);
+      cfg.dynamicSmemBytes = F_SMEM_BYTES;
+      cfg.stream = s;
+      cfg.attrs = attr;
+      cfg.numAttrs = m->use_pdl ? 1 : 0;
+      B200_CUDA(cudaLaunchKernelEx(&cfg, fc_sample_kernel, m->tc[L - 1].map_h[wr], m->map_w_fc, a));
+    }
     ++launches;
     m->trace_mark("fc_sample", s);
   }

@@ -61,6 +61,7 @@ struct b200gru_model {
   __nv_bfloat16 *onehot = nullptr;   // [bpad, kx]  layer-0 x operand
   __nv_bfloat16 *t0w = nullptr;      // [H/64][192][kx] layer-0 table as K-major weights
   CUtensorMap map_onehot, map_t0w, map_t0w_p;
+  bool use_pdl = true;               // programmatic dependent launch between the step kernels
   bool use_pairs = true;             // cta_group::2 layer kernel (B200GRU_CTA_PAIRS=0 disables)
   bool debug_logits = false;         // FC kernel also stores pre-softmax logits
   b200gru::TcLayer tc[B200GRU_MAX_LAYERS];

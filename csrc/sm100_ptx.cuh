@@ -239,6 +239,17 @@ __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// ------------------------------------------- programmatic dependent launch
+// wait: block until the kernel(s) this launch depends on have completed and
+// their memory is visible.  launch_dependents: allow the next kernel in the
+// stream to start its own prologue early.
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // ------------------------------------------------------- CTA pairs (2-SM MMA)
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
