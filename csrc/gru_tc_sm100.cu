@@ -85,6 +85,7 @@ struct LayerArgs {
   // counter there; the TMA producer of the consuming kernel waits on the
   // counter of a source rank right before it loads that rank's K-chunk.
   int tp_world, tp_rank;
+  int tp_debug;       // timing experiments only (results become wrong): 1 skip peer stores, 2 skip counter waits
   int kb_rank;        // k-blocks per source rank in a full-width operand
   int x_full;         // x operand is a full-width hidden buffer (layers >= 1)
   int col0;
@@ -182,12 +183,15 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
 //    h_out with coalesced 16-byte stores (a warp covers four full 128-byte
 //    rows) through the LSU, which keeps far more NVLink writes in flight than
 //    the TMA store path does (measured: ~1 GB/s per SM for remote TMA stores);
-//  * the counter bump that publishes a tile is deferred to the next tile (see
-//    epilogue_publish_prev): by then its stores have had a tile time to land.
-struct EpiState { int prev_m_tile; };
+//    each warp then hands the tile to the publisher warp through an mbarrier.
+struct PubRing {
+  uint64_t *full;    // [2] count 8: one arrive per epilogue warp, after its peer stores
+  uint64_t *empty;   // [2] count 1: publisher has read the slot
+  int *m_tile;       // [2]
+};
 __device__ __forceinline__ void epilogue_store_tile(const CUtensorMap *map_out, const LayerArgs &args,
                                                     uint8_t *stage_tile, int col, int m_tile,
-                                                    bool issuer, int tid, EpiState &st) {
+                                                    bool issuer, int tid, const PubRing &pub, int it) {
   fence_proxy_async_smem();                       // generic smem writes -> async proxy
   named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);   // the staged tile is complete
   if (issuer) {
@@ -197,28 +201,41 @@ __device__ __forceinline__ void epilogue_store_tile(const CUtensorMap *map_out, 
     tma_store_commit();
   }
   if (args.tp_world > 1) {
+    if (!(args.tp_debug & 1)) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int idx = tid + j * (L_EPI_WARPS * 32);  // 16-byte chunk of the 16 KB tile
-      const int r = idx >> 3, c = idx & 7;
-      const uint4 v = *reinterpret_cast<const uint4 *>(stage_tile + r * 128 + ((c ^ (r & 7)) << 4));
-      const size_t off = h_offset(m_tile * kTileM + r, col + c * 8, args.pw_log2, args.bpad);
-      for (int d = 0; d < args.tp_world; ++d)
-        if (d != args.tp_rank) *reinterpret_cast<uint4 *>(args.h_out_peer[d] + off) = v;
+      for (int j = 0; j < 4; ++j) {
+        const int idx = tid + j * (L_EPI_WARPS * 32);  // 16-byte chunk of the 16 KB tile
+        const int r = idx >> 3, c = idx & 7;
+        const uint4 v = *reinterpret_cast<const uint4 *>(stage_tile + r * 128 + ((c ^ (r & 7)) << 4));
+        const size_t off = h_offset(m_tile * kTileM + r, col + c * 8, args.pw_log2, args.bpad);
+        for (int d = 0; d < args.tp_world; ++d)
+          if (d != args.tp_rank) *reinterpret_cast<uint4 *>(args.h_out_peer[d] + off) = v;
+      }
     }
-    st.prev_m_tile = m_tile;
+    // hand over to the publisher: slot (it & 1), reused every second tile
+    const int slot = it & 1;
+    const uint32_t ph = (uint32_t)(it >> 1) & 1;
+    __syncwarp();
+    if ((tid & 31) == 0) {
+      mbar_wait(&pub.empty[slot], ph ^ 1);
+      if (tid == 0) pub.m_tile[slot] = m_tile;
+      mbar_arrive(&pub.full[slot]);  // release (CTA scope): orders this warp's peer stores
+    }
   }
 }
-// Called at the top of the next tile (and once after the last): every thread
-// fences its own remote stores of the previous tile system-wide, the epilogue
-// warps meet, then one thread bumps that tile's counter on every rank.
-__device__ __forceinline__ void epilogue_publish_prev(const LayerArgs &args, bool issuer,
-                                                      EpiState &st, bool need_barrier) {
-  if (args.tp_world > 1 && st.prev_m_tile >= 0) __threadfence_system();
-  if (need_barrier) named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
-  if (issuer && args.tp_world > 1 && st.prev_m_tile >= 0)
-    for (int d = 0; d < args.tp_world; ++d)
-      red_release_sys_add(args.signal_peer[d] + st.prev_m_tile, 1u);
+// Publisher (warp 3, one lane): for every tile of this CTA, once all epilogue
+// warps have issued their peer stores, fence system-wide — this is where the
+// NVLink write acknowledgements are waited for, off the epilogue's critical
+// path — and bump the tile's counter on every rank.
+__device__ __forceinline__ void publish_tile(const LayerArgs &args, const PubRing &pub, int it) {
+  const int slot = it & 1;
+  const uint32_t ph = (uint32_t)(it >> 1) & 1;
+  mbar_wait(&pub.full[slot], ph);
+  const int m_tile = pub.m_tile[slot];
+  mbar_arrive(&pub.empty[slot]);
+  __threadfence_system();
+  for (int d = 0; d < args.tp_world; ++d)
+    red_release_sys_add(args.signal_peer[d] + m_tile, 1u);
 }
 
 // ------------------------------------------------------------ TMA producer
@@ -249,7 +266,7 @@ __device__ __forceinline__ void produce_part(const CUtensorMap *map_a, const CUt
     const int kb0 = tp ? src * args.kb_rank : 0;
     bool fence = false;
     if (tp && src != args.tp_rank) {
-      tp_wait_counter(wait + src * args.flag_stride + m_tile, expect);
+      if (!(args.tp_debug & 2)) tp_wait_counter(wait + src * args.flag_stride + m_tile, expect);
       fence = true;  // remote generic-proxy writes -> this chunk's TMA reads
     }
     int kw = kb0 * TC_BLOCK_K;
@@ -300,6 +317,8 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
   uint64_t *tmem_full = bars + 2 * L_STAGES;       // [2]
   uint64_t *tmem_empty = bars + 2 * L_STAGES + 2;  // [2]
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * L_STAGES + 4);
+  const PubRing pub{bars + 2 * L_STAGES + 5, bars + 2 * L_STAGES + 7,
+                    reinterpret_cast<int *>(bars + 2 * L_STAGES + 9)};
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -319,6 +338,8 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], L_EPI_WARPS);  // one arrive per epilogue warp
+      mbar_init(&pub.full[i], L_EPI_WARPS);
+      mbar_init(&pub.empty[i], 1);
     }
     fence_mbar_init();
   }
@@ -403,6 +424,13 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       }
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
+  } else if (warp == 3) {
+    // ======================================= publisher (tensor parallel only)
+    if (args.tp_world > 1 && lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it)
+        publish_tile(args, pub, it);
+    }
   } else if (warp >= 4) {
     // ========================================================= epilogue
     // 8 warps: warp%4 picks the TMEM lane quarter (hardware rule), warp/4
@@ -414,7 +442,6 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
     uint32_t acc_phase = 0;
     uint8_t *stage_out = smem + L_STAGES * L_STAGE_BYTES + 1024;  // after the barrier block
     const bool issuer = (warp == 4 && lane == 0);
-    EpiState est{-1};
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int m_tile = tile / args.n_blocks;
@@ -438,10 +465,9 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
-      // the TMA store that read this staging buffer two tiles ago is done;
-      // publish the previous tile to the other tensor-parallel ranks
+      // the TMA store that read this staging buffer two tiles ago is done
       if (issuer) tma_store_wait_read<1>();
-      epilogue_publish_prev(args, issuer, est, true);
+      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
 
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
@@ -450,11 +476,10 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);  // TMEM stage back to the MMAs
-      epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, est);
+      epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, pub, it);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
     if (issuer) tma_store_wait<0>();  // smem must outlive the store's reads
-    epilogue_publish_prev(args, issuer, est, true);
   }
 
   tc_fence_before();
@@ -495,6 +520,8 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
   uint64_t *tmem_full = bars + 2 * P_STAGES;       // [2]      (each CTA its own)
   uint64_t *tmem_empty = bars + 2 * P_STAGES + 2;  // [2]      (leader's is used)
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * P_STAGES + 4);
+  const PubRing pub{bars + 2 * P_STAGES + 5, bars + 2 * P_STAGES + 7,
+                    reinterpret_cast<int *>(bars + 2 * P_STAGES + 9)};
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -519,6 +546,8 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], 2 * L_EPI_WARPS);  // epilogue warps of both CTAs
+      mbar_init(&pub.full[i], L_EPI_WARPS);
+      mbar_init(&pub.empty[i], 1);
     }
     fence_mbar_init();
   }
@@ -602,6 +631,13 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
         if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
       }
     }
+  } else if (warp == 3) {
+    // ======================================= publisher (tensor parallel only)
+    if (args.tp_world > 1 && lane == 0) {
+      int it = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it)
+        publish_tile(args, pub, it);
+    }
   } else if (warp >= 4) {
     // ======================================== epilogue (both CTAs, own rows)
     const int quarter = warp & 3;
@@ -611,7 +647,6 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     uint32_t acc_phase = 0;
     uint8_t *stage_out = smem + P_STAGES * P_STAGE_BYTES + 1024;  // after the barrier block
     const bool issuer = (warp == 4 && lane == 0);
-    EpiState est{-1};
     int it = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
       const int m2 = tile / args.n_blocks;
@@ -635,7 +670,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
       if (issuer) tma_store_wait_read<1>();
-      epilogue_publish_prev(args, issuer, est, true);
+      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
 
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
@@ -644,11 +679,10 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
-      epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, est);
+      epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, pub, it);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
     if (issuer) tma_store_wait<0>();  // smem must outlive the store's reads
-    epilogue_publish_prev(args, issuer, est, true);
   }
 
   tc_fence_before();
@@ -1159,6 +1193,7 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
       a.pw_log2 = m->pw_log2; a.bpad = m->bpad; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
       a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.x_full = l > 0;
+      { const char *e = getenv("B200GRU_TP_DEBUG"); a.tp_debug = e ? atoi(e) : 0; }
       a.col0 = R * Hs; a.flag_stride = mt_max;
       a.h_out_peer[0] = t.h[wr];
       if (W > 1) {
