@@ -694,11 +694,13 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
 }
 
 // ---------------------------------------------------------------------- FC
-constexpr int F_THREADS = 256;               // 4 role warps + 4 epilogue warps
+constexpr int F_EPI_WARPS = 8;               // two threads per name: each walks half of the columns
+constexpr int F_THREADS = (4 + F_EPI_WARPS) * 32;
 constexpr int F_B_BYTES_MAX = 256 * 128;     // 32 KB
 constexpr int F_STAGE_BYTES = TC_A_BYTES + F_B_BYTES_MAX;
 constexpr int F_STAGES = 4;
-constexpr int F_SMEM_BYTES = F_STAGES * F_STAGE_BYTES + 1024 + 256;
+// [align slack][stages][512 B barriers | 2 KB epilogue exchange]
+constexpr int F_SMEM_BYTES = 1024 + F_STAGES * F_STAGE_BYTES + 4096;
 
 struct FcArgs {
   int n, m_tiles, kb, H, C, T, step, eos, kx;  // kx = one-hot row length
@@ -733,7 +735,7 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_h); tma_prefetch_desc(&map_w); }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < F_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], F_EPI_WARPS); }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<TC_TMEM_COLS>(tmem_slot);
@@ -810,25 +812,34 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
   } else if (warp >= 4) {
+    // Two threads per name (same TMEM lane): half 0 (warps 4-7) owns columns
+    // [0, split), half 1 (warps 8-11) owns [split, C).  Partial sums and the
+    // second half's result cross over through a few words of shared memory.
     const int quarter = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const int rl = quarter * 32 + lane;           // row within the tile
+    const int split = ((C / 16 + 1) / 2) * 16;
+    const int cbeg = half == 0 ? 0 : split, cend = half == 0 ? split : C;
+    float *part_sum = reinterpret_cast<float *>(smem + F_STAGES * F_STAGE_BYTES + 512);  // [2][128]
+    int *part_sel = reinterpret_cast<int *>(part_sum + 2 * kTileM);                      // [128]
     int acc_stage = 0;
     uint32_t acc_phase = 0;
     const float kLog2e = 1.4426950408889634f;
     for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x) {
-      const int row = tile * kTileM + quarter * 32 + lane;
+      const int row = tile * kTileM + rl;
       const bool valid = row < args.n;
       const bool live = valid && args.alive[row] != 0;
       // this step's random float: fetched (possibly over NVLink from the root
       // rank's buffer — the MPI_Scatter of ref:636) before the accumulator wait
       const float r = live ? args.rfloats[(size_t)row * args.T + args.step] : 2.0f;
-      const int old_char = valid ? args.chars[row] : 0;
+      const int old_char = (valid && half == 0) ? args.chars[row] : 0;
       mbar_wait(&tmem_full[acc_stage], acc_phase);
       tc_fence_after();
       const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * TC_ACC_STRIDE;
       // pass 1: e_i = exp(f_i + b_i), kept in TMEM in place; four partial sums
       float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll 1
-      for (int c0 = 0; c0 < C; c0 += 16) {
+      for (int c0 = cbeg; c0 < cend; c0 += 16) {
         uint32_t v[16];
         tmem_ld16(t + c0, v);
         tmem_ld_wait();
@@ -849,25 +860,35 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
         tmem_st16(t + c0, v);
       }
       tmem_st_wait();
-      const float sum = (s0 + s1) + (s2 + s3);
-      // pass 2: first i with sum_{j<=i} p_j > r, p_j = e_j / sum (ref:322-333)
+      part_sum[half * kTileM + rl] = (s0 + s1) + (s2 + s3);
+      named_bar_sync(EPI_BAR_ID, F_EPI_WARPS * 32);
+      const float sum_lo = part_sum[rl], sum = sum_lo + part_sum[kTileM + rl];
+      // pass 2: first i with sum_{j<=i} p_j > r, p_j = e_j / sum (ref:322-333);
+      // the second half starts from the first half's share of the mass
       const float inv = 1.0f / sum;
-      float psum = 0.0f;
-      int sel = C - 1;
-      bool found = false;
+      float psum = half == 0 ? 0.0f : sum_lo * inv;
+      int sel = -1;
 #pragma unroll 1
-      for (int c0 = 0; c0 < C; c0 += 16) {
-        if (__all_sync(0xffffffffu, found || !live)) break;  // warp-uniform exit
+      for (int c0 = cbeg; c0 < cend; c0 += 16) {
+        if (__all_sync(0xffffffffu, sel >= 0 || !live)) break;  // warp-uniform exit
         uint32_t v[16];
         tmem_ld16(t + c0, v);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           psum = fmaf(__uint_as_float(v[i]), inv, psum);
-          if (!found && psum > r) { sel = c0 + i; found = true; }
+          if (sel < 0 && psum > r) sel = c0 + i;
         }
       }
-      if (valid) {
+      // accumulator drained: hand the TMEM stage back before the bookkeeping
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
+      if (half == 1) part_sel[rl] = sel;
+      named_bar_sync(EPI_BAR_ID, F_EPI_WARPS * 32);
+      if (half == 0 && valid) {
+        if (sel < 0) sel = part_sel[rl];
+        if (sel < 0) sel = C - 1;               // fallback n-1, ref:332
         char *orow = args.output + (size_t)row * (args.T + 1);
         if (args.step == 0)
           for (int l = 1; l <= args.T; ++l) orow[l] = 0;  // NUL pad, ref:643
@@ -881,9 +902,10 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
           if (sel == args.eos) args.alive[row] = 0;  // ref:881
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
+      // part_sum / part_sel are rewritten next tile only after the first
+      // barrier of that tile's pass 1 ... which every thread reaches after
+      // having read them here; one more barrier keeps that airtight
+      named_bar_sync(EPI_BAR_ID, F_EPI_WARPS * 32);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
   }
