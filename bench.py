@@ -33,7 +33,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--names-per-gpu", type=int, default=65536)
-    ap.add_argument("--ref-names-per-gpu", type=int, default=128,
+    ap.add_argument("--ref-names-per-gpu", type=int, default=32,
                     help="names per rank for the reference arm (its cost is strictly per-name serial)")
     ap.add_argument("--mode", default="tc", choices=["tc", "exact"])
     ap.add_argument("--dp", default="p2p", choices=["p2p", "nccl"])
