@@ -193,7 +193,15 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
   DeviceGuard guard(m->device);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   m->last_launches = 0;
-  if (n == 0 && !io->done_flag) return 0;
+  if (n == 0) {
+    // a rank with no names (N < ranks, ref:628 gives JPP = 0) still has to
+    // report completion so the root's gather wait can finish
+    if (io->done_flag && m->tp_world == 1) {
+      if (int rc = b200gru_signal_flag(io->done_flag, io->done_value, stream)) return rc;
+      m->last_launches = 1;
+    }
+    return 0;
+  }
   if (mode == B200GRU_MODE_EXACT) {
     if (m->tp_world > 1)
       return fail(B200GRU_ERR_ARG, "the fp32 exact path does not run tensor parallel");

@@ -49,7 +49,7 @@ def run_gpu(n_names: int, method: str):
     params = W.random_init(cfg, 11)
     rf = W.random_floats(n_names * cfg.max_len, 5)
     for mode in ("exact", "tc"):
-        gen = NameGenerator(cfg, params, device=local, max_batch=n_names, mode=mode)
+        gen = NameGenerator(cfg, params, device=local, max_batch=max(n_names, 8), mode=mode)
         comm = DPContext(cfg, local, n_names, method=method)
         gen.comm = comm
         for it in range(3):     # epochs reuse the flags

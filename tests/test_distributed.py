@@ -57,12 +57,13 @@ def test_logical_ranks_on_one_gpu_bit_identical(world, tiny_cfg, tiny_params):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("method", ["p2p", "nccl"])
-def test_real_ranks_p2p(method):
+@pytest.mark.parametrize("method,n", [("p2p", 1001), ("nccl", 1001), ("p2p", 1)])
+def test_real_ranks_p2p(method, n):
+    """n = 1 with >= 2 ranks: JPP = 0, every rank is idle and the row stays zero."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")
     world = min(torch.cuda.device_count(), 8)
-    r = _torchrun(world, "gpu", 1001, method, timeout=600)
+    r = _torchrun(world, "gpu", n, method, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("GPU_DP_OK") == 2
 

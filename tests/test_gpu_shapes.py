@@ -51,3 +51,10 @@ def test_too_many_names_is_an_error(tiny_cfg, tiny_params):
     with NameGenerator(tiny_cfg, tiny_params, device=0, max_batch=8) as g:
         with pytest.raises(ValueError):
             g.generate_device(torch.zeros(1000, device="cuda"), 9)
+
+
+def test_zero_names_is_a_no_op(tiny_cfg, tiny_params):
+    with NameGenerator(tiny_cfg, tiny_params, device=0, max_batch=8) as g:
+        for mode in ("exact", "tc"):
+            out = g.generate(0, torch.zeros(0), mode=mode)
+            assert out.shape == (0, tiny_cfg.max_len + 1)
