@@ -131,3 +131,23 @@ def test_trace_reports_every_launch(gen_tiny, tiny_cfg):
     assert len(tr) == gen_tiny.last_launches == 1 + tiny_cfg.max_len * (tiny_cfg.num_layers + 1)
     assert [k for k, _ in tr[:4]] == ["init", "layer0", "layerN", "fc_sample"]
     assert all(t >= 0 for _, t in tr)
+
+
+def test_tc_character_distribution_matches_exact(gen_tiny, tiny_cfg):
+    """Sampling amplifies 1-ulp CDF differences, so bf16 names are compared
+    statistically: two-sample chi-square on the character histograms of the
+    tensor-core and the exact path (same random floats)."""
+    n = 1024
+    r = W.random_floats(n * tiny_cfg.max_len, 26)
+    tc = gen_tiny.generate(n, r, mode="tc")[:, : tiny_cfg.max_len].reshape(-1).long()
+    ex = gen_tiny.generate(n, r, mode="exact")[:, : tiny_cfg.max_len].reshape(-1).long()
+    C = tiny_cfg.num_char
+    a = torch.bincount(tc, minlength=C).double()
+    b = torch.bincount(ex, minlength=C).double()
+    keep = (a + b) > 0
+    chi2 = (((a - b) ** 2) / (a + b))[keep].sum().item()
+    dof = int(keep.sum().item()) - 1
+    # identical streams of random floats make the two samples strongly dependent,
+    # so chi2 is far below dof; dof + 4*sqrt(2*dof) would already be generous
+    assert chi2 < dof + 4 * (2 * dof) ** 0.5, (chi2, dof)
+    assert (tc == ex).double().mean() > 0.9
