@@ -69,9 +69,24 @@ def _compile_one(src: Path, digest: str, verbose: bool) -> Path:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every source under csrc/ for sm_100a and link libb200gru.so."""
+    """Compile every source under csrc/ for sm_100a and link libb200gru.so.
+
+    Serialised across processes with a file lock: under torchrun every rank
+    imports the package at the same moment."""
+    import fcntl
     OBJ_DIR.mkdir(parents=True, exist_ok=True)
     LIB_DIR.mkdir(parents=True, exist_ok=True)
+    with open(OBJ_DIR / ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not needs_build():
+                return LIB_PATH          # another process built it while we waited
+            return _build_locked(force, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(force: bool, verbose: bool) -> Path:
     digest = _headers_digest()
     srcs = sources()
     if force:
