@@ -48,7 +48,8 @@ struct DeviceGuard {
 
 __global__ void wait_flags_kernel(const uint32_t *flags, int n, uint32_t value) {
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    while (sm100::ld_acquire_sys(flags + i) != value) __nanosleep(200);
+    // epochs only grow: '>=' (wrap-safe) tolerates a peer that is already a call ahead
+    while ((int32_t)(sm100::ld_acquire_sys(flags + i) - value) < 0) __nanosleep(200);
   }
   __syncthreads();
   __threadfence_system();
@@ -216,7 +217,8 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
     // Replay a captured graph when nothing about the call varies: no
     // completion flag (its value changes per call), no tensor-parallel
     // counters, no tracing.
-    const bool graphable = m->use_graph && m->tp_world == 1 && !io->done_flag && !m->trace_on;
+    const bool graphable = m->use_graph && m->tp_world == 1 && !io->done_flag && !io->ready_flag &&
+                           !m->trace_on;
     if (!graphable) return tc_generate(m, n, io, s);
     for (auto &g : m->graphs)
       if (g.n == n && g.rfloats == io->rfloats && g.output == io->output &&

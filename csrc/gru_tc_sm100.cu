@@ -1274,6 +1274,11 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
       ++launches;
       m->trace_mark(l == 0 ? "layer0" : "layerN", s);
     }
+    if (step == 0 && io->ready_flag) {  // the floats are first needed here
+      if (int rc = b200gru_wait_flags(io->ready_flag, 1, io->ready_value, s)) return rc;
+      ++launches;
+      m->trace_mark("wait_floats", s);
+    }
     FcArgs a{};
     a.n = n; a.m_tiles = m_tiles; a.kb = H / TC_BLOCK_K; a.H = H; a.C = C; a.T = T;
     a.step = step; a.eos = c.eos; a.kx = m->kx;

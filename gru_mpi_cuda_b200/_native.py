@@ -22,7 +22,8 @@ class CIo(ctypes.Structure):
     """Mirror of `b200gru_io`."""
 
     _fields_ = [("rfloats", c_void_p), ("output", c_void_p),
-                ("done_flag", c_void_p), ("done_value", c_uint32)]
+                ("done_flag", c_void_p), ("done_value", c_uint32),
+                ("ready_flag", c_void_p), ("ready_value", c_uint32)]
 
 
 def _declare(lib):

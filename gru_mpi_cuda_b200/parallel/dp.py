@@ -52,6 +52,8 @@ class DPContext:
             self.out = SymmBuffer(self.out_bytes, device, group)
             self.flags = SymmBuffer(self.flag_bytes, device, group)
         self._host_out = None
+        self._copy_stream = None
+        self._epoch_host = torch.zeros(64, dtype=torch.int32).pin_memory() if torch.cuda.is_available() else None
         self.extra_launches = 0
 
     # root-side views
@@ -75,27 +77,38 @@ class DPContext:
         flags_root = self._root(self.flags)
         launches = 0
         with torch.cuda.device(self.device):
+            main = torch.cuda.current_stream(self.device)
             if self.rank == 0:
+                # The floats go up on a side stream and are announced with a flag;
+                # every rank (the root included) waits for that flag only right
+                # before its first sampling kernel, so the first character's GRU
+                # kernels overlap the host-to-device copy.
+                if self._copy_stream is None:
+                    self._copy_stream = torch.cuda.Stream(device=self.device)
+                cs = self._copy_stream
+                cs.wait_stream(main)  # the previous call (all ranks done reading) is behind us
+                cstream = ctypes.c_void_p(cs.cuda_stream)
                 if random_floats is not None:  # None: reuse the floats already on the device
                     rf = random_floats.reshape(-1)[: n_names * T]
                     if rf.dtype != torch.float32 or rf.device.type != "cpu":
                         raise ValueError("random_floats must be a host float32 tensor on the root rank")
                     _native.check(self.lib.b200gru_memcpy_async(ctypes.c_void_p(self.rf.local_ptr), rf.data_ptr(),
-                                                                rf.numel() * 4, 1, stream), "H2D floats")
+                                                                rf.numel() * 4, 1, cstream), "H2D floats")
+                # announce with a 4-byte copy (no kernel: a spinning wait kernel and a
+                # signalling kernel on one GPU are not guaranteed to be co-scheduled)
+                slot = self._epoch_host[e % self._epoch_host.numel():][:1]
+                slot.fill_(e)
+                _native.check(self.lib.b200gru_memcpy_async(ctypes.c_void_p(flags_root), slot.data_ptr(), 4, 1,
+                                                            cstream), "ready flag")
                 covered = sl.jpp * self.world if self.drop_remainder else n_names
                 if covered < n_names:  # rows nobody generates stay zero (ref:640)
                     _native.check(self.lib.b200gru_memset_async(
                         ctypes.c_void_p(self.out.local_ptr + covered * (T + 1)), 0,
                         (n_names - covered) * (T + 1), stream))
-                _native.check(self.lib.b200gru_signal_flag(ctypes.c_void_p(flags_root), e, stream))
-                launches += 1
-            else:
-                # wait for "floats are in place" (acquire-poll of rank 0's flag over NVLink)
-                _native.check(self.lib.b200gru_wait_flags(ctypes.c_void_p(flags_root), 1, e, stream))
-                launches += 1
             io = _native.CIo(self._root(self.rf) + sl.start * T * 4,
                              self._root(self.out) + sl.start * (T + 1),
-                             flags_root + 4 * (1 + self.rank), e)
+                             flags_root + 4 * (1 + self.rank), e,
+                             flags_root, e)  # ready flag: acquire-polled (over NVLink off the root)
             m = gen.mode if mode is None else {"exact": 0, "fp32": 0, "tc": 1, "bf16": 1}[mode]
             _native.check(self.lib.b200gru_generate(gen._h, m, sl.count, ctypes.byref(io), stream), "generate")
             launches += self.lib.b200gru_last_launch_count(gen._h)

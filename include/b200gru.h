@@ -139,12 +139,18 @@ int64_t b200gru_model_device_bytes(const b200gru_model *m);
  * (root buffer + start*max_len), `output` at this rank's first row
  * (root buffer + start*(max_len+1)).  If `done_flag` is non-null the last
  * kernel release-stores `done_value` to it (system scope) after its output
- * rows are written. */
+ * rows are written.  If `ready_flag` is non-null, the random floats are only
+ * read once `*ready_flag == ready_value` (acquire, system scope): the wait sits
+ * right before the first sampling kernel, so the GRU kernels of the first
+ * character already run while the root's host-to-device copy of the floats is
+ * still in flight. */
 typedef struct b200gru_io {
   const float *rfloats;
   char *output;
   uint32_t *done_flag;
   uint32_t done_value;
+  const uint32_t *ready_flag;
+  uint32_t ready_value;
 } b200gru_io;
 
 /* namegen() equivalent for one rank's slice (ref:627-890, minus the MPI
@@ -167,7 +173,7 @@ int b200gru_model_set_trace(b200gru_model *m, int on);
 int b200gru_model_get_trace(b200gru_model *m, float *ms, const char **names,
                             int max_spans);
 
-/* Kernel that spins (ld.acquire.sys) until flags[i] == value for all i<n;
+/* Kernel that spins (ld.acquire.sys) until flags[i] >= value (wrap-safe) for all i<n;
  * rank 0 runs it after its own generate to complete the gather. */
 int b200gru_wait_flags(const uint32_t *flags, int n, uint32_t value,
                        void *stream);
