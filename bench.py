@@ -29,7 +29,7 @@ METRIC = "generated names/sec (whole box, device-timed, max over ranks)"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--names-per-gpu", type=int, default=65536)
@@ -174,6 +174,7 @@ def run_ours(args):
         barrier()
         launches_per_step = gen.last_launches
         t_wall0 = time.perf_counter()
+        t_epoch0 = time.time()
         for a, b in evs:
             flush.fill_(2)          # evict L2 between timed iterations (outside the event pair)
             a.record()
@@ -181,12 +182,14 @@ def run_ours(args):
             b.record()
         barrier()
         t_wall = time.perf_counter() - t_wall0
+        t_epoch1 = time.time()
+        time.sleep(0.05)  # let the sampler flush its last rows
     ms_local = sum(a.elapsed_time(b) for a, b in evs)
     ms_t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms_total = ms_t.item()
-    clocks = cs.summary()
+    clocks = cs.summary(t_epoch0, t_epoch1)
 
     # ---- end to end through the public API: pinned host floats in, host bytes out
     for _ in range(2):

@@ -6,7 +6,7 @@ import statistics
 import subprocess
 import tempfile
 
-_FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+_FIELDS = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
            "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
            "clocks_event_reasons.sw_power_cap")
 
@@ -35,27 +35,36 @@ class ClockSampler:
             except Exception:
                 self.proc.kill()
 
-    def summary(self) -> dict:
+    def summary(self, t0: float | None = None, t1: float | None = None) -> dict:
+        """Median SM clock and throttle reasons.  With `t0`/`t1` (time.time()
+        stamps of the timed region) only samples taken inside it count as
+        "under load"; otherwise the top half of observed power does."""
+        import datetime
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if not self.tmp:
             return out
         self.tmp.flush()
         rows = [l.strip().split(", ") for l in open(self.tmp.name) if l.strip()]
-        sm, mx, pw = [], [], []
+        ts, sm, mx, pw, rs = [], [], [], [], []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        seen = set()
         for r in rows:
             try:
-                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+                t = datetime.datetime.strptime(r[0].strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                c, m, p = float(r[1]), float(r[2]), float(r[3])
             except (ValueError, IndexError):
                 continue
-            for name, v in zip(names, r[3:7]):
-                if v.strip().lower().startswith("active"):
-                    seen.add(name)
-        if sm:
-            # "under load": samples in the top half of observed power
-            thr = (max(pw) + min(pw)) / 2 if pw else 0
-            loaded = [c for c, p in zip(sm, pw) if p >= thr] or sm
-            out.update(sm_mhz=statistics.median(loaded), sm_max_mhz=max(mx), power_w_max=max(pw),
-                       reasons=sorted(seen), samples=len(sm))
+            ts.append(t); sm.append(c); mx.append(m); pw.append(p)
+            rs.append({n for n, v in zip(names, r[4:8]) if v.strip().lower().startswith("active")})
+        if not sm:
+            return out
+        idx = [i for i, t in enumerate(ts) if t0 is not None and t1 is not None and t0 <= t <= t1]
+        how = "inside the timed region"
+        if not idx:
+            thr = (max(pw) + min(pw)) / 2
+            idx = [i for i, p in enumerate(pw) if p >= thr] or list(range(len(sm)))
+            how = "top half of observed power"
+        seen = set().union(*[rs[i] for i in idx])
+        out.update(sm_mhz=statistics.median(sm[i] for i in idx), sm_max_mhz=max(mx),
+                   power_w_max=max(pw[i] for i in idx), reasons=sorted(seen), samples=len(idx),
+                   samples_total=len(sm), under_load=how)
         return out
