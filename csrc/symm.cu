@@ -127,3 +127,17 @@ extern "C" int b200gru_p2p_write_bench(void *const *dsts, int ndst, const void *
   B200_CUDA(cudaGetLastError());
   return 0;
 }
+
+extern "C" int b200gru_stream_synchronize(void *stream) {
+  B200_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int b200gru_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}

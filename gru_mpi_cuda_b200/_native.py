@@ -68,6 +68,8 @@ def _declare(lib):
         "b200gru_memset_async": (c_int, [c_void_p, c_int, c_size_t, c_void_p]),
         "b200gru_signal_flag": (c_int, [c_void_p, c_uint32, c_void_p]),
         "b200gru_can_access_peer": (c_int, [c_int, c_int]),
+        "b200gru_stream_synchronize": (c_int, [c_void_p]),
+        "b200gru_device_count": (c_int, []),
         "b200gru_gru_cell_fp32": (c_int, [c_void_p] * 7 + [c_int, c_int, c_int, c_void_p]),
         "b200gru_p2p_write_bench": (c_int, [P(c_void_p), c_int, c_void_p, ctypes.c_longlong, c_int,
                                             ctypes.c_longlong, c_int, c_void_p]),

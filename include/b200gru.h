@@ -194,6 +194,9 @@ int b200gru_memset_async(void *dst, int value, size_t bytes, void *stream);
 /* st.release.sys of `value` to `flag` after prior work on `stream`. */
 int b200gru_signal_flag(uint32_t *flag, uint32_t value, void *stream);
 int b200gru_can_access_peer(int device, int peer);
+/* For C callers that do not link the CUDA runtime themselves. */
+int b200gru_stream_synchronize(void *stream);
+int b200gru_device_count(void); /* 0 when there is no usable GPU / driver */
 
 /* Diagnostic: write `rows` x `row_bytes` (row pitch `pitch`) from `src` to
  * `ndst` destination buffers with coalesced 16-byte stores; tools/p2p_bench.py
