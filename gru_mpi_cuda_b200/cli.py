@@ -32,6 +32,10 @@ def main(argv=None) -> int:
     ap.add_argument("--params", help="weight file (headerless fp32, reference layout)")
     ap.add_argument("--random-init", action="store_true", help="use deterministic random weights")
     ap.add_argument("--make-weights", metavar="PATH", help="write random-init weights to PATH and exit")
+    ap.add_argument("--import-torch", nargs=2, metavar=("STATE.pt", "OUT.bin"),
+                    help="convert a torch state dict (embedding/gru/fc keys) to the reference weight file and exit")
+    ap.add_argument("--export-torch", nargs=2, metavar=("IN.bin", "STATE.pt"),
+                    help="convert a reference weight file to a torch state dict and exit")
     ap.add_argument("--n", type=int, default=16, help="number of names (N)")
     ap.add_argument("--seed", type=int, default=0, help="seed of the random floats (rng_seed)")
     ap.add_argument("--out", help="write the N x (MAX_LEN+1) byte matrix here")
@@ -46,6 +50,17 @@ def main(argv=None) -> int:
     a = ap.parse_args(argv)
     cfg = _cfg(a)
 
+    if a.import_torch:
+        src, dst = a.import_torch
+        sd = torch.load(src, map_location="cpu", weights_only=True)
+        W.save(dst, W.from_torch_state(cfg, sd))
+        print(f"wrote {W.param_count(cfg) * 4} bytes to {dst}")
+        return 0
+    if a.export_torch:
+        src, dst = a.export_torch
+        torch.save(W.to_torch_state(cfg, W.load(src, cfg)), dst)
+        print(f"wrote torch state dict to {dst}")
+        return 0
     if a.make_weights:
         W.save(a.make_weights, W.random_init(cfg, a.seed))
         print(f"wrote {W.param_count(cfg) * 4} bytes to {a.make_weights}")

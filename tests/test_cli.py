@@ -37,3 +37,19 @@ def test_make_weights_then_generate_on_cpu(tmp_path):
 def test_cli_requires_weights():
     r = _run("--n", "4", "--mode", "cpu")
     assert r.returncode != 0
+
+
+def test_torch_state_dict_round_trip_through_the_cli(tmp_path):
+    from gru_mpi_cuda_b200 import GRUConfig
+    from gru_mpi_cuda_b200.models import TorchNameGen
+    from gru_mpi_cuda_b200.utils import weights as W
+    cfg = GRUConfig.tiny()
+    model = TorchNameGen(cfg)                       # stock torch init
+    pt, w, pt2 = tmp_path / "m.pt", tmp_path / "w.bin", tmp_path / "m2.pt"
+    torch.save(model.state_dict(), pt)
+    assert _run("--import-torch", str(pt), str(w), *TINY).returncode == 0
+    assert w.stat().st_size == W.param_count(cfg) * 4
+    assert _run("--export-torch", str(w), str(pt2), *TINY).returncode == 0
+    sd = torch.load(pt2, weights_only=True)
+    for k, v in model.state_dict().items():
+        assert torch.equal(sd[k], v), k
