@@ -192,12 +192,15 @@ def run_ours(args):
     clocks = cs.summary(t_epoch0, t_epoch1)
 
     # ---- end to end through the public API: pinned host floats in, host bytes out
+    # like the reference's caller-allocated `output` (namegensf.cu:624-627): a pinned host buffer
+    out_host = torch.empty(n_total, T + 1, dtype=torch.uint8).pin_memory() if (rank == 0 and comm is None) else None
+    e2e_kw = {"out": out_host} if comm is None else {}
     for _ in range(2):
-        gen.generate(n_total, rf_host)
+        gen.generate(n_total, rf_host, **e2e_kw)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        out = gen.generate(n_total, rf_host)
+        out = gen.generate(n_total, rf_host, **e2e_kw)
     barrier()
     e2e_s = time.perf_counter() - t0
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)

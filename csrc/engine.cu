@@ -169,7 +169,10 @@ int b200gru_model_destroy(b200gru_model *m) {
   DeviceGuard guard(m->device);
   cudaError_t first = cudaDeviceSynchronize();
   for (cudaEvent_t e : m->trace_ev) cudaEventDestroy(e);
-  for (auto &g : m->graphs) cudaGraphExecDestroy(g.exec);
+  for (auto &g : m->graphs) {
+    cudaGraphExecDestroy(g.exec);
+    if (g.exec_tail) cudaGraphExecDestroy(g.exec_tail);
+  }
   if (m->cap_stream) cudaStreamDestroy(m->cap_stream);
   for (void *p : m->allocs) {
     cudaError_t e = cudaFree(p);
@@ -220,52 +223,56 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
     const bool graphable = m->use_graph && m->tp_world == 1 && !io->done_flag && !io->ready_flag &&
                            !m->trace_on;
     if (!graphable) return tc_generate(m, n, io, s);
+    const bool split = io->ready_event != nullptr;  // two graphs with an event wait in between
+    auto launch = [&](b200gru_model::GraphEntry &g) -> int {
+      g.last_use = ++m->graph_clock;
+      m->last_launches = g.launches;
+      B200_CUDA(cudaGraphLaunch(g.exec, s));
+      if (g.exec_tail) {
+        B200_CUDA(cudaStreamWaitEvent(s, static_cast<cudaEvent_t>(io->ready_event), 0));
+        B200_CUDA(cudaGraphLaunch(g.exec_tail, s));
+      }
+      return 0;
+    };
     for (auto &g : m->graphs)
       if (g.n == n && g.rfloats == io->rfloats && g.output == io->output &&
-          g.logits == m->debug_logits) {
-        g.last_use = ++m->graph_clock;
-        m->last_launches = g.launches;
-        B200_CUDA(cudaGraphLaunch(g.exec, s));
-        return 0;
-      }
+          g.logits == m->debug_logits && (g.exec_tail != nullptr) == split)
+        return launch(g);
     // Capture on a private stream (the caller's may be the legacy default
     // stream, which cannot be captured); the graph is launched on the caller's.
     if (!m->cap_stream)
       B200_CUDA(cudaStreamCreateWithFlags(&m->cap_stream, cudaStreamNonBlocking));
-    cudaGraph_t graph = nullptr;
-    B200_CUDA(cudaStreamBeginCapture(m->cap_stream, cudaStreamCaptureModeThreadLocal));
-    int rc = tc_generate(m, n, io, m->cap_stream);
-    cudaError_t ce = cudaStreamEndCapture(m->cap_stream, &graph);
-    if (rc) {
-      if (graph) cudaGraphDestroy(graph);
-      return rc;
-    }
-    if (ce != cudaSuccess || !graph) {  // capture not possible here: run eagerly
-      cudaGetLastError();
-      m->use_graph = false;
-      return tc_generate(m, n, io, s);
-    }
     b200gru_model::GraphEntry e;
-    ce = cudaGraphInstantiate(&e.exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (ce != cudaSuccess) {
-      cudaGetLastError();
-      m->use_graph = false;
-      return tc_generate(m, n, io, s);
+    for (int half = 0; half < (split ? 2 : 1); ++half) {
+      cudaGraph_t graph = nullptr;
+      B200_CUDA(cudaStreamBeginCapture(m->cap_stream, cudaStreamCaptureModeThreadLocal));
+      int rc = tc_generate(m, n, io, m->cap_stream, split ? half + 1 : 0);
+      cudaError_t ce = cudaStreamEndCapture(m->cap_stream, &graph);
+      cudaGraphExec_t exec = nullptr;
+      if (!rc && ce == cudaSuccess && graph) ce = cudaGraphInstantiate(&exec, graph, 0);
+      if (graph) cudaGraphDestroy(graph);
+      if (rc || ce != cudaSuccess || !exec) {
+        if (e.exec) cudaGraphExecDestroy(e.exec);
+        if (rc) return rc;
+        cudaGetLastError();  // capture not possible here: run eagerly from now on
+        m->use_graph = false;
+        return tc_generate(m, n, io, s);
+      }
+      (half == 0 ? e.exec : e.exec_tail) = exec;
+      e.launches += m->last_launches;
     }
     e.n = n; e.rfloats = io->rfloats; e.output = io->output; e.logits = m->debug_logits;
-    e.launches = m->last_launches; e.last_use = ++m->graph_clock;
     if (m->graphs.size() >= 8) {  // evict the least recently used
       size_t victim = 0;
       for (size_t i = 1; i < m->graphs.size(); ++i)
         if (m->graphs[i].last_use < m->graphs[victim].last_use) victim = i;
       cudaGraphExecDestroy(m->graphs[victim].exec);
+      if (m->graphs[victim].exec_tail) cudaGraphExecDestroy(m->graphs[victim].exec_tail);
       m->graphs[victim] = e;
-    } else {
-      m->graphs.push_back(e);
+      return launch(m->graphs[victim]);
     }
-    B200_CUDA(cudaGraphLaunch(e.exec, s));
-    return 0;
+    m->graphs.push_back(e);
+    return launch(m->graphs.back());
   }
   return fail(B200GRU_ERR_ARG, "unknown mode %d", mode);
 }

@@ -257,6 +257,8 @@ int exact_generate(b200gru_model *m, int n, const b200gru_io *io,
       if (int rc = exact_sgemm_tn(x, m->P(ix.w_fc()), m->logits, nb, C, H, s))
         return rc;
       ++launches;
+      if (base == 0 && step == 0 && io->ready_event)
+        B200_CUDA(cudaStreamWaitEvent(s, static_cast<cudaEvent_t>(io->ready_event), 0));
       if (base == 0 && step == 0 && io->ready_flag) {  // the floats are first needed here
         if (int rc = b200gru_wait_flags(io->ready_flag, 1, io->ready_value, s)) return rc;
         ++launches;

@@ -1177,7 +1177,12 @@ static int num_sms(int device) {
   return n;
 }
 
-int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
+// part: 0 = the whole call; 1 = only what runs before the random floats are
+// needed (reset + the first character's layer kernels); 2 = the rest.  The
+// engine captures 1 and 2 as separate graphs when the caller supplies a
+// `ready_event`, and waits for the event between them.
+int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, int part) {
+  const bool head = part != 2, tail = part != 1;
   const b200gru_config &c = m->cfg;
   const int H = c.hidden, C = c.num_char, T = c.max_len, L = c.num_layers;
   // tp_fake: profile ONE rank's share of a tensor-parallel model on a single GPU
@@ -1190,15 +1195,15 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
   const int rows = m_tiles * kTileM;
   const int mt_max = m->bpad / kTileM;
   const uint32_t per_round = (uint32_t)(Hs / kUnitBlock);  // counter bumps per (source, m-tile)
-  m->trace_begin(s);
-  if (W > 1) {
+  if (head) m->trace_begin(s);
+  if (head && W > 1) {
     if (!m->tp_bound) return fail(B200GRU_ERR_STATE, "tensor-parallel model: call b200gru_tp_bind first");
     // nobody may touch our buffers for this call until every peer is done with the last one
     tp_wait_epoch_kernel<<<1, 32, 0, s>>>(m->tp_sync[R], W, m->tp_epoch);
     ++launches;
     m->trace_mark("tp_wait_epoch", s);
   }
-  {
+  if (head) {
     size_t total = (size_t)rows * m->kx;
     tc_init_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(
         m->chars, m->alive, m->onehot, n, rows, m->kx, c.sos);
@@ -1208,6 +1213,7 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
   for (int step = 0; step < T; ++step) {
     const int rd = step & 1, wr = rd ^ 1;  // ping-pong hidden buffers
     for (int l = 0; l < L; ++l) {
+      if (!(step == 0 ? head : tail)) continue;
       TcLayer &t = m->tc[l];
       LayerArgs a{};
       a.n = n; a.m_tiles = m_tiles; a.n_blocks = Hs / kUnitBlock;
@@ -1274,6 +1280,9 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
       ++launches;
       m->trace_mark(l == 0 ? "layer0" : "layerN", s);
     }
+    if (!tail) break;  // part 1 ends before the first sampling kernel
+    if (step == 0 && part == 0 && io->ready_event)
+      B200_CUDA(cudaStreamWaitEvent(s, static_cast<cudaEvent_t>(io->ready_event), 0));
     if (step == 0 && io->ready_flag) {  // the floats are first needed here
       if (int rc = b200gru_wait_flags(io->ready_flag, 1, io->ready_value, s)) return rc;
       ++launches;
@@ -1307,14 +1316,14 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s) {
     ++launches;
     m->trace_mark("fc_sample", s);
   }
-  if (W > 1) {
+  if (tail && W > 1) {
     m->tp_epoch += 1;
     TpPeers peers{};
     for (int r = 0; r < W; ++r) peers.p[r] = m->tp_sync[r] + R;
     tp_signal_epoch_kernel<<<1, 32, 0, s>>>(peers, W, m->tp_epoch);
     ++launches;
   }
-  if (io->done_flag) {
+  if (tail && io->done_flag) {
     tc_signal_done_kernel<<<1, 1, 0, s>>>(io->done_flag, io->done_value);
     ++launches;
   }

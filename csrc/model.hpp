@@ -88,6 +88,7 @@ struct b200gru_model {
     void *output = nullptr;
     bool logits = false;
     cudaGraphExec_t exec = nullptr;
+    cudaGraphExec_t exec_tail = nullptr;  // second half when the call is split at `ready_event`
     int launches = 0;
     uint64_t last_use = 0;
   };
@@ -133,7 +134,7 @@ int gru_cell_fp32_run(const float *x, const float *h_in, const float *w_ih,
                       float *scratch, cudaStream_t s);
 // tensor-core path (gru_tc_sm100.cu)
 int tc_prepare(b200gru_model *m);
-int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s);
+int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, int part = 0);
 size_t tp_shared_bytes(const b200gru_model *m);
 int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases);
 // TMA descriptor helper (tma_host.cu)

@@ -23,7 +23,8 @@ class CIo(ctypes.Structure):
 
     _fields_ = [("rfloats", c_void_p), ("output", c_void_p),
                 ("done_flag", c_void_p), ("done_value", c_uint32),
-                ("ready_flag", c_void_p), ("ready_value", c_uint32)]
+                ("ready_flag", c_void_p), ("ready_value", c_uint32),
+                ("ready_event", c_void_p)]
 
 
 def _declare(lib):

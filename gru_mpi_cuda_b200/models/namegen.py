@@ -71,10 +71,13 @@ class NameGenerator:
         self._out_dev = torch.zeros(self.max_batch, cfg.max_len + 1, dtype=torch.uint8, device=dev)
         self._out_host = torch.zeros(self.max_batch, cfg.max_len + 1, dtype=torch.uint8).pin_memory()
         self.last_launches = 0
+        self._copy_stream = None
+        self._ready_ev = None
 
     # ------------------------------------------------------------------ core
     def generate_device(self, rfloats_dev: torch.Tensor, n: int, out_dev: torch.Tensor | None = None,
-                        mode: str | None = None, done_flag_ptr: int = 0, done_value: int = 0) -> torch.Tensor:
+                        mode: str | None = None, done_flag_ptr: int = 0, done_value: int = 0,
+                        ready_event: torch.cuda.Event | None = None) -> torch.Tensor:
         """Generate `n` names from device-resident floats; asynchronous on the
         current stream.  `rfloats_dev` / `out_dev` may live on a peer GPU."""
         cfg = self.cfg
@@ -82,7 +85,8 @@ class NameGenerator:
             raise ValueError(f"n={n} > max_batch={self.max_batch}")
         if out_dev is None:
             out_dev = self._out_dev
-        io = _native.CIo(rfloats_dev.data_ptr(), out_dev.data_ptr(), done_flag_ptr or None, done_value)
+        io = _native.CIo(rfloats_dev.data_ptr(), out_dev.data_ptr(), done_flag_ptr or None, done_value,
+                         None, 0, ready_event.cuda_event if ready_event is not None else None)
         stream = torch.cuda.current_stream(self.device).cuda_stream
         m = self.mode if mode is None else _MODES[mode]
         _native.check(self._lib.b200gru_generate(self._h, m, n, ctypes.byref(io), ctypes.c_void_p(stream)),
@@ -90,8 +94,13 @@ class NameGenerator:
         self.last_launches = self._lib.b200gru_last_launch_count(self._h)
         return out_dev[:n]
 
-    def generate(self, n_names: int, random_floats: torch.Tensor, mode: str | None = None) -> torch.Tensor:
-        """namegen(): host floats in, host `uint8[n_names, max_len+1]` out."""
+    def generate(self, n_names: int, random_floats: torch.Tensor, mode: str | None = None,
+                 out: torch.Tensor | None = None) -> torch.Tensor:
+        """namegen(): host floats in, host `uint8[n_names, max_len+1]` out.
+
+        `out` plays the reference's caller-allocated `char *output`
+        (`namegensf.cu:624-627`): a pinned host `uint8[n_names, max_len+1]` tensor
+        that is filled and returned instead of a fresh copy."""
         if self.comm is not None:
             return self.comm.generate(self, n_names, random_floats, mode=mode)
         cfg = self.cfg
@@ -101,12 +110,21 @@ class NameGenerator:
             raise ValueError(f"random_floats has {rf.numel()} values, need {need}")
         sl = partition(n_names, 1, 0)
         with torch.cuda.device(self.device):
-            self._rf_dev[:need].copy_(rf[:need], non_blocking=True)
-            out = self.generate_device(self._rf_dev, sl.count, mode=mode)
-            host = self._out_host[:n_names]
-            host.copy_(out, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-        return host.clone()
+            main = torch.cuda.current_stream()
+            # the floats go up on a side stream; the kernels only wait for them
+            # (an event) right before the first sampling kernel
+            if self._copy_stream is None:
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+                self._ready_ev = torch.cuda.Event()
+            self._copy_stream.wait_stream(main)
+            with torch.cuda.stream(self._copy_stream):
+                self._rf_dev[:need].copy_(rf[:need], non_blocking=True)
+                self._ready_ev.record(self._copy_stream)
+            rows = self.generate_device(self._rf_dev, sl.count, mode=mode, ready_event=self._ready_ev)
+            host = self._out_host[:n_names] if out is None else out
+            host.copy_(rows, non_blocking=True)
+            main.synchronize()
+        return host.clone() if out is None else host
 
     def enable_logits_tap(self, on: bool = True) -> None:
         """Make the tensor-core FC kernel store its logits too (slow; tests only)."""

@@ -151,6 +151,8 @@ typedef struct b200gru_io {
   uint32_t done_value;
   const uint32_t *ready_flag;
   uint32_t ready_value;
+  void *ready_event; /* same idea within one process: a cudaEvent_t recorded
+                        after the upload of the floats on another stream */
 } b200gru_io;
 
 /* namegen() equivalent for one rank's slice (ref:627-890, minus the MPI
