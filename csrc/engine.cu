@@ -11,6 +11,8 @@
 // pointer ref:1017); nothing is allocated in generate.
 #include <cstdlib>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "model.hpp"
 #include "sm100_ptx.cuh"
 
@@ -197,6 +199,12 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
   DeviceGuard guard(m->device);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   m->last_launches = 0;
+  // NVTX range around the host side of the call (header-only NVTX3: a no-op
+  // unless a profiler is attached); the reference has no instrumentation at all
+  struct NvtxScope {
+    explicit NvtxScope(const char *name) { nvtxRangePushA(name); }
+    ~NvtxScope() { nvtxRangePop(); }
+  } nvtx(mode == B200GRU_MODE_TC ? "b200gru_generate[tc]" : "b200gru_generate[exact]");
   if (n == 0) {
     // a rank with no names (N < ranks, ref:628 gives JPP = 0) still has to
     // report completion so the root's gather wait can finish
