@@ -48,6 +48,8 @@ using namespace sm100;
 constexpr int TC_BLOCK_K = 64;               // 128 bytes of bf16 per row
 constexpr int TC_A_BYTES = kTileM * 128;     // 16 KB
 constexpr int TC_TMEM_COLS = 512;
+constexpr uint32_t kEpiSleepNs = 200;        // back-off of the epilogue's accumulator wait
+constexpr uint32_t kProdSleepNs = 50;        // back-off of the producer's free-slot wait
 constexpr int TC_ACC_STRIDE = 256;           // TMEM columns per accumulator
 
 // ------------------------------------------------------------------ layers
@@ -276,7 +278,7 @@ __device__ __forceinline__ void produce_part(const CUtensorMap *map_a, const CUt
       co += (kw >> args.pw_log2) * args.bpad;
     }
     for (int jj = 0; jj < chunk_len; ++jj) {
-      mbar_wait(&empty_bar[ring.stage], ring.phase ^ 1);
+      mbar_wait_relaxed(&empty_bar[ring.stage], ring.phase ^ 1, kProdSleepNs);
       if (elect_one()) {
         uint8_t *sa = smem + ring.stage * STAGE_BYTES;
         uint8_t *sb = sa + TC_A_BYTES;
@@ -469,7 +471,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       if (issuer) tma_store_wait_read<1>();
       named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
 
-      mbar_wait(&tmem_full[acc_stage], acc_phase);
+      mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
       tc_fence_after();
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
       gate_epilogue(t, hq, bias4, stage_tile, r, half);
@@ -672,7 +674,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       if (issuer) tma_store_wait_read<1>();
       named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
 
-      mbar_wait(&tmem_full[acc_stage], acc_phase);
+      mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
       tc_fence_after();
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
       gate_epilogue(t, hq, bias4, stage_tile, r, half);
@@ -833,7 +835,7 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
       // rank's buffer — the MPI_Scatter of ref:636) before the accumulator wait
       const float r = live ? args.rfloats[(size_t)row * args.T + args.step] : 2.0f;
       const int old_char = (valid && half == 0) ? args.chars[row] : 0;
-      mbar_wait(&tmem_full[acc_stage], acc_phase);
+      mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
       tc_fence_after();
       const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * TC_ACC_STRIDE;
       // pass 1: e_i = exp(f_i + b_i), kept in TMEM in place; four partial sums

@@ -77,6 +77,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
   }
 }
 
+// Wait with a back-off between probes: for roles that have slack (epilogue
+// warps waiting for an accumulator, the TMA producer waiting for a free slot).
+// A bare try_wait loop re-issues every ~60 cycles; eight epilogue warps doing
+// that are half of a kernel's issued instructions, all of it spent spinning.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity, uint32_t ns) {
+  while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
+
 // sub-block barrier over `nthreads` threads (bar.sync id, n)
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
