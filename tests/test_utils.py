@@ -20,7 +20,7 @@ def _fake_sampler(rows):
 def test_clock_summary_uses_the_timed_window():
     now = time.time()
     rows = [(now + 0.02 * i, 1965 if i < 5 else 1320 + i, 200 if i < 5 else 950, i >= 5) for i in range(12)]
-    s = _fake_sampler(rows).summary(now + 0.1, now + 0.3)
+    s = _fake_sampler(rows).summary(now + 0.09, now + 0.3)
     assert s["under_load"] == "inside the timed region"
     assert s["samples"] == 7 and s["samples_total"] == 12
     assert 1320 <= s["sm_mhz"] <= 1340 and s["sm_max_mhz"] == 1965
