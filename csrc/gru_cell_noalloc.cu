@@ -19,8 +19,17 @@
 //     op needs zeroed scratch — both GEMMs overwrite every element they later
 //     read — so no clearing is done.
 //   * the first call on each device looks the array's device address up
-//     (cudaGetSymbolAddress).  Make that first call during set-up, before any
-//     stream capture begins.
+//     (cudaGetSymbolAddress; with CUDA's lazy module loading this is also the
+//     moment the 4 MiB array appears on that GPU).  Make that first call during
+//     set-up, before any stream capture begins.
+//   * the scratch used is the CURRENT device's copy, and the kernels run on
+//     `stream`: the current device must be the one that owns `stream` and the
+//     seven operand buffers.  Device pointers that belong to another GPU are
+//     refused with B200GRU_ERR_ARG (checked with cudaPointerGetAttributes,
+//     which allocates nothing) instead of failing later with a launch error.
+//   * operands only need the natural 4-byte alignment of float; 16-byte
+//     aligned rows (pointer and in_dim/hidden multiples of 4) take the faster
+//     vector loads.
 // No counterpart in the reference.
 #include <mutex>
 
@@ -76,6 +85,27 @@ extern "C" int b200gru_gru_cell_fp32_noalloc(
                 "scratch, the built-in buffer holds %zu; use a smaller batch or "
                 "b200gru_gru_cell_fp32",
                 batch, hidden, need * sizeof(float), kScratchBytes);
+  // every operand must live on the device whose scratch (and stream) is used
+  {
+    int cur = -1;
+    B200_CUDA(cudaGetDevice(&cur));
+    const void *ops[7] = {x, h_in, w_ih, w_hh, b_ih, b_hh, h_out};
+    static const char *const names[7] = {"x", "h_in", "w_ih", "w_hh", "b_ih", "b_hh", "h_out"};
+    for (int i = 0; i < 7; ++i) {
+      if (reinterpret_cast<uintptr_t>(ops[i]) % alignof(float))
+        return fail(B200GRU_ERR_ARG, "gru_cell_fp32_noalloc: %s is not 4-byte aligned", names[i]);
+      cudaPointerAttributes at{};
+      if (cudaPointerGetAttributes(&at, ops[i]) != cudaSuccess) {
+        cudaGetLastError();
+        continue;  // not known to the runtime (e.g. a foreign allocator): cannot be checked here
+      }
+      if (at.type == cudaMemoryTypeDevice && at.device != cur)
+        return fail(B200GRU_ERR_ARG,
+                    "gru_cell_fp32_noalloc: %s lives on device %d but device %d is current; make the "
+                    "operands' device current (the built-in scratch is per device)",
+                    names[i], at.device, cur);
+    }
+  }
   float *scratch = nullptr;
   if (int rc = scratch_for_current_device(&scratch)) return rc;
   return gru_cell_fp32_run(x, h_in, w_ih, w_hh, b_ih, b_hh, h_out, batch, in_dim,

@@ -40,7 +40,11 @@ sgemm_tn_kernel(const float *__restrict__ A, const float *__restrict__ W,
 
   const int lrow = tid / 4;        // 0..63
   const int lk = (tid % 4) * 4;    // 0,4,8,12
-  const bool vec_ok = (K % 4 == 0);
+  // float4 loads need 16-byte aligned rows: K % 4 == 0 AND aligned base pointers
+  // (operands are often `params + offset`, and offsets such as num_char*emb_dim
+  // need not be multiples of 4 floats)
+  const bool vec_ok = (K % 4 == 0) &&
+                      (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(W)) & 15) == 0);
   for (int k0 = 0; k0 < K; k0 += SG_BK) {
     // load A tile (64 x 16) and W tile (64 x 16), transposed into smem
     {

@@ -87,7 +87,6 @@ struct LayerArgs {
   // counter there; the TMA producer of the consuming kernel waits on the
   // counter of a source rank right before it loads that rank's K-chunk.
   int tp_world, tp_rank;
-  int tp_debug;       // timing experiments only (results become wrong): 1 skip peer stores, 2 skip counter waits
   int kb_rank;        // k-blocks per source rank in a full-width operand
   int x_full;         // x operand is a full-width hidden buffer (layers >= 1)
   int col0;
@@ -203,16 +202,14 @@ __device__ __forceinline__ void epilogue_store_tile(const CUtensorMap *map_out, 
     tma_store_commit();
   }
   if (args.tp_world > 1) {
-    if (!(args.tp_debug & 1)) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int idx = tid + j * (L_EPI_WARPS * 32);  // 16-byte chunk of the 16 KB tile
-        const int r = idx >> 3, c = idx & 7;
-        const uint4 v = *reinterpret_cast<const uint4 *>(stage_tile + r * 128 + ((c ^ (r & 7)) << 4));
-        const size_t off = h_offset(m_tile * kTileM + r, col + c * 8, args.pw_log2, args.bpad);
-        for (int d = 0; d < args.tp_world; ++d)
-          if (d != args.tp_rank) *reinterpret_cast<uint4 *>(args.h_out_peer[d] + off) = v;
-      }
+    for (int j = 0; j < 4; ++j) {
+      const int idx = tid + j * (L_EPI_WARPS * 32);  // 16-byte chunk of the 16 KB tile
+      const int r = idx >> 3, c = idx & 7;
+      const uint4 v = *reinterpret_cast<const uint4 *>(stage_tile + r * 128 + ((c ^ (r & 7)) << 4));
+      const size_t off = h_offset(m_tile * kTileM + r, col + c * 8, args.pw_log2, args.bpad);
+      for (int d = 0; d < args.tp_world; ++d)
+        if (d != args.tp_rank) *reinterpret_cast<uint4 *>(args.h_out_peer[d] + off) = v;
     }
     // hand over to the publisher: slot (it & 1), reused every second tile
     const int slot = it & 1;
@@ -268,7 +265,7 @@ __device__ __forceinline__ void produce_part(const CUtensorMap *map_a, const CUt
     const int kb0 = tp ? src * args.kb_rank : 0;
     bool fence = false;
     if (tp && src != args.tp_rank) {
-      if (!(args.tp_debug & 2)) tp_wait_counter(wait + src * args.flag_stride + m_tile, expect);
+      tp_wait_counter(wait + src * args.flag_stride + m_tile, expect);
       fence = true;  // remote generic-proxy writes -> this chunk's TMA reads
     }
     int kw = kb0 * TC_BLOCK_K;
@@ -1045,10 +1042,13 @@ static size_t tp_h_bytes(const b200gru_model *m) {
 static size_t tp_counter_bytes(const b200gru_model *m) {
   return (size_t)m->tp_world * (m->bpad / kTileM) * sizeof(uint32_t);
 }
+static size_t tp_counter_stride(const b200gru_model *m) {  // bytes between counter blocks
+  return (tp_counter_bytes(m) + 255) / 256 * 256;
+}
 size_t tp_shared_bytes(const b200gru_model *m) {
   const int L = m->cfg.num_layers;
   size_t b = (size_t)L * 2 * tp_h_bytes(m);
-  b += (size_t)L * 2 * ((tp_counter_bytes(m) + 255) / 256 * 256);
+  b += (size_t)L * 2 * tp_counter_stride(m);
   b += 256;
   return b;
 }
@@ -1067,7 +1067,7 @@ int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
   B200_REQUIRE(m->tp_world > 1, "model was not created for tensor parallelism");
   const int L = m->cfg.num_layers;
   const size_t hb = tp_h_bytes(m);
-  const size_t cb = (tp_counter_bytes(m) + 255) / 256 * 256;
+  const size_t cb = tp_counter_stride(m);
   const size_t off_cnt = (size_t)L * 2 * hb;
   const size_t off_sync = off_cnt + (size_t)L * 2 * cb;
   for (int r = 0; r < m->tp_world; ++r) {
@@ -1204,6 +1204,10 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
     tp_wait_epoch_kernel<<<1, 32, 0, s>>>(m->tp_sync[R], W, m->tp_epoch);
     ++launches;
     m->trace_mark("tp_wait_epoch", s);
+    // Counters are per call: they were zeroed at the end of the previous call
+    // (see below), so the expected values only depend on this call's own
+    // launches — not on how many m-tiles earlier calls happened to touch.
+    for (int l = 0; l < L; ++l) m->tp_rounds[l][0] = m->tp_rounds[l][1] = 0;
   }
   if (head) {
     size_t total = (size_t)rows * m->kx;
@@ -1223,7 +1227,6 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
       a.pw_log2 = m->pw_log2; a.bpad = m->bpad; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
       a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.x_full = l > 0;
-      { const char *e = getenv("B200GRU_TP_DEBUG"); a.tp_debug = e ? atoi(e) : 0; }
       a.col0 = R * Hs; a.flag_stride = mt_max;
       a.h_out_peer[0] = t.h[wr];
       if (W > 1) {
@@ -1319,6 +1322,12 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
     m->trace_mark("fc_sample", s);
   }
   if (tail && W > 1) {
+    // Zero this rank's counters before announcing the end of the call.  Every
+    // bump a peer sends here is waited for by one of our kernels in the same
+    // step (the layer above, or FC for the top layer), so once our last FC
+    // kernel is done no bump is in flight; peers start bumping for the next
+    // call only after they have seen the epoch signal that follows.
+    B200_CUDA(cudaMemsetAsync(m->tp_cnt[R][0][0], 0, (size_t)L * 2 * tp_counter_stride(m), s));
     m->tp_epoch += 1;
     TpPeers peers{};
     for (int r = 0; r < W; ++r) peers.p[r] = m->tp_sync[r] + R;

@@ -55,8 +55,6 @@ def _compile_one(src: Path, digest: str, verbose: bool) -> Path:
     cmd = [nvcc(), *ARCH_FLAGS, *COMMON]
     if src.suffix == ".cu":
         cmd += CU_FLAGS
-    else:
-        cmd += ["-x", "cu"] if False else []
     cmd += ["-c", str(src), "-o", str(obj)]
     res = subprocess.run(cmd, capture_output=True, text=True)
     log = OBJ_DIR / (src.name + ".log")

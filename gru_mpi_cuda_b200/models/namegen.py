@@ -102,7 +102,7 @@ class NameGenerator:
         (`namegensf.cu:624-627`): a pinned host `uint8[n_names, max_len+1]` tensor
         that is filled and returned instead of a fresh copy."""
         if self.comm is not None:
-            return self.comm.generate(self, n_names, random_floats, mode=mode)
+            return self.comm.generate(self, n_names, random_floats, mode=mode, out=out)
         cfg = self.cfg
         need = n_names * cfg.max_len
         rf = random_floats.reshape(-1)

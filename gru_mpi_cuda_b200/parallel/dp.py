@@ -61,13 +61,26 @@ class DPContext:
         return buf.ptrs[0]
 
     def generate(self, gen, n_names: int, random_floats: torch.Tensor | None, mode: str | None = None,
-                 to_host: bool = True):
+                 to_host: bool = True, out: torch.Tensor | None = None):
         """Collective: every rank calls it; only rank 0's `random_floats` is
-        read and only rank 0 gets the `[n_names, max_len+1]` result."""
+        read and only rank 0 gets the `[n_names, max_len+1]` result.
+
+        `out` (root only) is the reference's caller-allocated `char *output`
+        (`namegensf.cu:624-627`): a pinned host `uint8[n_names, max_len+1]`
+        tensor that receives the rows directly (one device-to-host copy, no
+        staging copy) and is returned."""
         if n_names > self.max_total:
             raise ValueError(f"n_names={n_names} > max_names_total={self.max_total}")
         if self.method == "nccl":
-            return self._generate_nccl(gen, n_names, random_floats, mode, to_host)
+            res = self._generate_nccl(gen, n_names, random_floats, mode, to_host)
+            if out is not None and res is not None:
+                out.copy_(res)
+                return out
+            return res
+        if out is not None and self.rank == 0:
+            if (out.dtype != torch.uint8 or out.device.type != "cpu" or not out.is_contiguous()
+                    or out.numel() != n_names * (self.cfg.max_len + 1)):
+                raise ValueError("out must be a contiguous host uint8 tensor of n_names*(max_len+1) bytes")
         cfg = self.cfg
         T = cfg.max_len
         sl = partition(n_names, self.world, self.rank, self.drop_remainder)
@@ -118,12 +131,18 @@ class DPContext:
                 launches += 1
                 if to_host:
                     nb = n_names * (T + 1)
-                    if self._host_out is None or self._host_out.numel() < nb:
-                        self._host_out = torch.empty(self.out_bytes, dtype=torch.uint8).pin_memory()
-                    _native.check(self.lib.b200gru_memcpy_async(self._host_out.data_ptr(),
-                                                                ctypes.c_void_p(self.out.local_ptr), nb, 2, stream))
+                    if out is not None:
+                        dst = out
+                    else:
+                        if self._host_out is None or self._host_out.numel() < nb:
+                            self._host_out = torch.empty(self.out_bytes, dtype=torch.uint8).pin_memory()
+                        dst = self._host_out
+                    _native.check(self.lib.b200gru_memcpy_async(dst.data_ptr(), ctypes.c_void_p(self.out.local_ptr),
+                                                                nb, 2, stream))
                     torch.cuda.current_stream(self.device).synchronize()
-                    result = self._host_out[:nb].view(n_names, T + 1).clone()
+                    # without a caller buffer the rows are copied out of the reused staging buffer
+                    result = out.view(n_names, T + 1) if out is not None else \
+                        self._host_out[:nb].view(n_names, T + 1).clone()
             elif to_host:
                 torch.cuda.current_stream(self.device).synchronize()
         gen.last_launches = launches

@@ -45,7 +45,12 @@ class TPContext:
         peers = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(p) for p in self.shared.ptrs])
         _native.check(self.lib.b200gru_tp_bind(self.gen._h, ctypes.c_void_p(self.shared.local_ptr), peers), "tp_bind")
         # root-owned I/O, read / written in place by every rank's kernels (as in DP)
-        self.rf = SymmBuffer(max_batch * T * 4, device, group)
+        # two halves, used alternately: a peer may still be reading call e's floats
+        # (every rank's sampling kernels load them over NVLink) while the root
+        # already uploads call e+1's; half (e & 1) is only rewritten for call e+2,
+        # whose upload is ordered after the epoch fence of call e+1 on the root's stream
+        self.rf_half = (max_batch * T * 4 + 255) // 256 * 256
+        self.rf = SymmBuffer(2 * self.rf_half, device, group)
         self.flags = SymmBuffer(256, device, group)
         self.out = torch.zeros(max_batch, T + 1, dtype=torch.uint8, device=torch.device("cuda", device))
         self._host_out = torch.empty(max_batch, T + 1, dtype=torch.uint8).pin_memory()
@@ -67,13 +72,19 @@ class TPContext:
             if self.rank == 0:
                 if random_floats is not None:
                     rf = random_floats.reshape(-1)[: n_names * T]
-                    _native.check(self.lib.b200gru_memcpy_async(ctypes.c_void_p(self.rf.local_ptr), rf.data_ptr(),
-                                                                rf.numel() * 4, 1, stream))
+                    _native.check(self.lib.b200gru_memcpy_async(
+                        ctypes.c_void_p(self.rf.local_ptr + (e & 1) * self.rf_half), rf.data_ptr(),
+                        rf.numel() * 4, 1, stream))
+                elif e > 1:  # reuse the previous call's floats: bring them over to this call's half
+                    _native.check(self.lib.b200gru_memcpy_async(
+                        ctypes.c_void_p(self.rf.local_ptr + (e & 1) * self.rf_half),
+                        ctypes.c_void_p(self.rf.local_ptr + ((e - 1) & 1) * self.rf_half),
+                        n_names * T * 4, 3, stream))
                 _native.check(self.lib.b200gru_signal_flag(ctypes.c_void_p(flag_root), e, stream))
             else:
                 _native.check(self.lib.b200gru_wait_flags(ctypes.c_void_p(flag_root), 1, e, stream))
             launches += 1
-            io = _native.CIo(self.rf.ptrs[0], self.out.data_ptr(), None, 0)
+            io = _native.CIo(self.rf.ptrs[0] + (e & 1) * self.rf_half, self.out.data_ptr(), None, 0)
             _native.check(self.lib.b200gru_generate(self.gen._h, 1, n_names, ctypes.byref(io), stream), "generate")
             launches += self.lib.b200gru_last_launch_count(self.gen._h)
             self.gen.last_launches = launches

@@ -64,7 +64,8 @@ class ClockSampler:
             idx = [i for i, p in enumerate(pw) if p >= thr] or list(range(len(sm)))
             how = "top half of observed power"
         seen = set().union(*[rs[i] for i in idx])
-        out.update(sm_mhz=statistics.median(sm[i] for i in idx), sm_max_mhz=max(mx),
+        out.update(sm_mhz=statistics.median(sm[i] for i in idx), sm_mhz_min=min(sm[i] for i in idx),
+                   sm_max_mhz=max(mx),
                    power_w_max=max(pw[i] for i in idx), reasons=sorted(seen), samples=len(idx),
                    samples_total=len(sm), under_load=how)
         return out

@@ -232,7 +232,11 @@ int b200gru_gru_cell_fp32(const float *x, const float *h_in, const float *w_ih,
  *   - 2*batch*3*hidden*4 bytes must fit, else B200GRU_ERR_ARG with a message;
  *   - all calls on one GPU share the array: calls that may overlap there race;
  *   - the first call on a device resolves the array's address; make it during
- *     set-up, before any stream capture.
+ *     set-up, before any stream capture;
+ *   - the current device must be the one that owns `stream` and all seven
+ *     buffers (the scratch is the current device's copy): device pointers of
+ *     another GPU are refused with B200GRU_ERR_ARG.
+ * Operands need only 4-byte alignment (16-byte aligned rows run faster).
  * Asynchronous on `stream`; inputs and outputs are the caller's, as above. */
 #define B200GRU_NOALLOC_SCRATCH_BYTES (4u << 20)
 int b200gru_gru_cell_fp32_noalloc(const float *x, const float *h_in,

@@ -36,6 +36,18 @@ def test_shapes_exact_and_tc(cfg, n):
     assert (tc[:, -1] == 0).all()
 
 
+def test_exact_path_with_unaligned_weight_offsets():
+    """num_char*emb_dim = 135 floats puts every later tensor of the weight file on
+    an address that is not 16-byte aligned while K % 4 == 0 for hidden = 32: the
+    SGEMM must then take its scalar loads, not fault on a float4."""
+    cfg = GRUConfig(num_char=27, emb_dim=5, hidden=32, num_layers=2, max_len=4, sos=0, eos=1)
+    p = W.random_init(cfg, 3)
+    for n in (1, 77):
+        r = W.random_floats(n * cfg.max_len, 4)
+        with NameGenerator(cfg, p, device=0, max_batch=n, mode="exact") as g:
+            assert torch.equal(g.generate(n, r), oracle.generate(cfg, p, r))
+
+
 def test_unsupported_tc_shape_falls_back_loudly():
     """hidden not a multiple of 64: the tensor-core path refuses, the exact path runs."""
     cfg = GRUConfig(num_char=32, emb_dim=16, hidden=40, num_layers=2, max_len=3)
