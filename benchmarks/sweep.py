@@ -30,6 +30,9 @@ def main():
     ap.add_argument("--sizes", default="1024,4096,16384,65536,262144,1048576")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--dp", default="p2p")
+    ap.add_argument("--path", default="auto", choices=["auto", "multi", "persistent"],
+                    help="tensor-core kernel path (auto: persistent kernel for small calls)")
+    ap.add_argument("--persist-max", type=int, default=-1, help="auto: largest call (names per GPU) for the persistent kernel")
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -41,6 +44,7 @@ def main():
     sizes = [int(x) for x in a.sizes.split(",")]
     nmax = max(sizes)
     gen = NameGenerator(cfg, W.random_init(cfg, 1), device=local, max_batch=(nmax + world - 1) // world, mode="tc")
+    gen.set_path(a.path, a.persist_max)
     comm = None
     if world > 1:
         comm = DPContext(cfg, local, nmax, method=a.dp)
@@ -77,7 +81,7 @@ def main():
         if world > 1:
             dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
         if rank == 0:
-            row = {"n_names": n, "gpus": world, "ms_device": ms.item(), "names_per_sec_device": n / (ms.item() / 1e3),
+            row = {"n_names": n, "gpus": world, "path": a.path, "launches": gen.last_launches, "ms_device": ms.item(), "names_per_sec_device": n / (ms.item() / 1e3),
                    "ms_e2e": e2e.item() * 1e3, "names_per_sec_e2e": n / e2e.item()}
             rows.append(row)
             print(json.dumps(row), flush=True)

@@ -97,6 +97,8 @@ int create_impl(b200gru_model *m, const float *params_host) {
                                  "multiple of 16 in [16,256] (H=%d, world=%d, C=%d)", H, m->tp_world, C);
   if (m->tc_ok)
     if (int rc = tc_prepare(m)) return rc;
+  if (m->tc_ok)
+    if (int rc = persist_prepare(m)) return rc;
   B200_CUDA(cudaDeviceSynchronize());
   return 0;
 }
@@ -141,6 +143,11 @@ int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
   {
     const char *e = getenv("B200GRU_GRAPH");
     m->use_graph = !(e && e[0] == '0');
+  }
+  {
+    // kernel path for tensor-core mode: auto picks the persistent kernel for small batches
+    if (const char *e = getenv("B200GRU_PATH")) m->ps_path = atoi(e);
+    if (const char *e = getenv("B200GRU_PERSIST_MAX")) m->ps_max_n = atoi(e);
   }
   {
     const char *e = getenv("B200GRU_TP_FAKE");
@@ -225,6 +232,14 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
                   "tensor-core mode needs hidden %% 64 == 0 and num_char a "
                   "multiple of 16 in [16,256] (got H=%d, C=%d)",
                   m->cfg.hidden, m->cfg.num_char);
+    // Small batches: the whole call is one persistent kernel (weights resident
+    // in shared memory, flags handled in-kernel).  Large batches: one launch per
+    // layer per character, replayed as a CUDA graph.
+    if (m->ps_path == 2 && !m->ps_ok)
+      return fail(B200GRU_ERR_ARG, "the persistent kernel cannot run this model (H=%d, L=%d) on this GPU",
+                  m->cfg.hidden, m->cfg.num_layers);
+    if (m->ps_ok && (m->ps_path == 2 || (m->ps_path == 0 && n <= m->ps_max_n)))
+      return persist_generate(m, n, io, s);
     // Replay a captured graph when nothing about the call varies: no
     // completion flag (its value changes per call), no tensor-parallel
     // counters, no tracing.
@@ -293,6 +308,14 @@ int b200gru_model_set_debug(b200gru_model *m, int logits_tap) {
   B200_REQUIRE(m, "null model");
   m->debug_logits = logits_tap != 0;
   return 0;
+}
+
+int b200gru_model_set_path(b200gru_model *m, int path, int persist_max_names) {
+  B200_REQUIRE(m, "null model");
+  B200_REQUIRE(path >= 0 && path <= 2, "path must be 0 (auto), 1 (multi-launch) or 2 (persistent)");
+  m->ps_path = path;
+  if (persist_max_names >= 0) m->ps_max_n = persist_max_names;
+  return m->ps_ok ? 1 : 0;
 }
 
 int b200gru_model_set_trace(b200gru_model *m, int on) {

@@ -69,6 +69,18 @@ struct b200gru_model {
   CUtensorMap map_w_fc;
   const float *b_fc = nullptr;    // into params
 
+  // --- persistent weight-stationary kernel (gru_persist_sm100.cu): one launch
+  // per generate for small batches
+  bool ps_ok = false;
+  int ps_path = 0;                   // 0 auto (by batch size), 1 multi-launch only, 2 persistent only
+  int ps_max_n = 512;                // auto: use the persistent kernel up to this many names
+  int ps_smem = 0, ps_stages = 0, ps_pairs = 0, ps_fc_max = 0;
+  __nv_bfloat16 *ps_w_ih[B200GRU_MAX_LAYERS] = {};   // packed [H/16][n|r|z x 16][H]
+  __nv_bfloat16 *ps_w_hh[B200GRU_MAX_LAYERS] = {};   // packed [H/16][r|z|n x 16][H]
+  CUtensorMap ps_map_w_ih[B200GRU_MAX_LAYERS], ps_map_w_hh[B200GRU_MAX_LAYERS];
+  __nv_bfloat16 *ps_t0p = nullptr;   // [H/16][C][n|r|z][16] folded layer-0 input table
+  uint32_t *ps_sync = nullptr;       // per-tile counters + live counts, zeroed per call
+
   // --- tensor parallelism over the hidden dimension (tp_world == 1: off)
   int tp_world = 1, tp_rank = 0;
   bool tp_bound = false;
@@ -135,6 +147,9 @@ int gru_cell_fp32_run(const float *x, const float *h_in, const float *w_ih,
 // tensor-core path (gru_tc_sm100.cu)
 int tc_prepare(b200gru_model *m);
 int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, int part = 0);
+// persistent path (gru_persist_sm100.cu)
+int persist_prepare(b200gru_model *m);
+int persist_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s);
 size_t tp_shared_bytes(const b200gru_model *m);
 int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases);
 // TMA descriptor helper (tma_host.cu)

@@ -130,6 +130,14 @@ class NameGenerator:
         """Make the tensor-core FC kernel store its logits too (slow; tests only)."""
         _native.check(self._lib.b200gru_model_set_debug(self._h, 1 if on else 0))
 
+    def set_path(self, path: str = "auto", persist_max_names: int = -1) -> bool:
+        """Kernel path of the tensor-core mode: "auto" (persistent kernel for
+        calls of at most `persist_max_names` names, multi-launch above),
+        "multi" or "persistent".  Returns whether the persistent kernel can run
+        this model at all (its weight slices must fit in shared memory)."""
+        code = {"auto": 0, "multi": 1, "persistent": 2}[path]
+        return bool(_native.check(self._lib.b200gru_model_set_path(self._h, code, persist_max_names), "set_path"))
+
     def set_trace(self, on: bool = True) -> None:
         """Record a CUDA event after every launch of the tensor-core path."""
         _native.check(self._lib.b200gru_model_set_trace(self._h, 1 if on else 0))

@@ -168,6 +168,20 @@ int b200gru_model_set_debug(b200gru_model *m, int logits_tap);
 int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
                          void *stream);
 
+/* Kernel path of tensor-core mode.  The reference's name loop, step loop and 51
+ * launches per character (ref:649, :661, :664-873) exist here in two shapes:
+ *   multi-launch (1): one launch per GRU layer per character + FC/sample, weight
+ *     tiles streamed from L2 — fastest for large batches;
+ *   persistent (2): ONE cooperative launch per call; every CTA pair keeps its
+ *     16-unit slice of all recurrent weights in shared memory for the whole call,
+ *     layers / FC / sampling are chained by per-tile counters — fastest for
+ *     small batches.  Needs all slices to fit (e.g. H <= 1024 with 2 layers).
+ * path 0 (default) picks persistent when it is available and
+ * n <= persist_max_names (default 512; < 0 leaves the threshold unchanged).
+ * Returns 1 if the persistent kernel is available for this model, 0 if not.
+ * Environment: B200GRU_PATH, B200GRU_PERSIST_MAX set the defaults at create. */
+int b200gru_model_set_path(b200gru_model *m, int path, int persist_max_names);
+
 /* Tracing (absent in the reference): with set_trace(m, 1) the tensor-core
  * generate records a CUDA event after every launch; get_trace returns the
  * per-launch device times of the last call (synchronises on its last event). */

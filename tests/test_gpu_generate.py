@@ -124,10 +124,12 @@ def test_eos_stops_and_pads(tiny_cfg):
 def test_trace_reports_every_launch(gen_tiny, tiny_cfg):
     n = 300
     r = W.random_floats(n * tiny_cfg.max_len, 25)
+    gen_tiny.set_path("multi")      # the per-layer launches; the persistent path is one span
     gen_tiny.set_trace(True)
     gen_tiny.generate(n, r, mode="tc")
     tr = gen_tiny.trace()
     gen_tiny.set_trace(False)
+    gen_tiny.set_path("auto")
     assert len(tr) == gen_tiny.last_launches == 1 + tiny_cfg.max_len * (tiny_cfg.num_layers + 1)
     assert [k for k, _ in tr[:4]] == ["init", "layer0", "layerN", "fc_sample"]
     assert all(t >= 0 for _, t in tr)

@@ -141,7 +141,8 @@ def test_noalloc_first_call_is_the_only_one_that_costs_memory():
     code = textwrap.dedent("""
         import ctypes, sys, torch
         sys.path.insert(0, %r)
-        from tests.test_zz_no_alloc import _lib, _case
+        sys.path.insert(0, %r + "/tests")
+        from test_zz_no_alloc import _lib, _case
         from ctypes import c_void_p
         lib = _lib()
         B, E, H = 64, 64, 128
@@ -159,7 +160,7 @@ def test_noalloc_first_call_is_the_only_one_that_costs_memory():
         f2, _ = torch.cuda.mem_get_info()
         torch.cuda.synchronize()
         print(f0 - f1, f1 - f2)
-    """ % str(__import__("pathlib").Path(__file__).resolve().parent.parent))
+    """ % ((str(__import__("pathlib").Path(__file__).resolve().parent.parent),) * 2))
     res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stderr[-2000:]
     first, second = map(int, res.stdout.split()[-2:])
