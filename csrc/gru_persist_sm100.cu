@@ -49,19 +49,20 @@ constexpr int PS_N = 48;                     // UMMA N over the pair
 constexpr int PS_KB_BYTES = PS_ROWS * 128;   // one 64-wide k-block of a CTA's slice (3 swizzle atoms)
 constexpr int PS_A_BYTES = kTileM * 128;     // 16 KB: 128 names x 64 k
 constexpr int PS_ACC_COLS = 64;              // [ n_i | r | z | n_h ] x 16 units
-constexpr int PS_TMEM_COLS = 128;            // two accumulator stages
+constexpr int PS_ACC_STAGES = 8;             // accumulator stages: the MMA warp may run 8 tiles ahead of the epilogue
+constexpr int PS_TMEM_COLS = PS_ACC_STAGES * PS_ACC_COLS;  // all 512 columns
 constexpr int PS_THREADS = 384;
 constexpr int PS_EPI_WARPS = 8;
 constexpr int PS_MAX_STAGES = 8;
-constexpr int PS_FC_STAGES = 4;
+constexpr int PS_FC_STAGES = 6;
 constexpr int PS_EPI_BAR = 1;
-constexpr uint32_t kSpinNs = 32;
+constexpr uint32_t kSpinNs = 0;   // waits on the per-step critical path poll back to back
 
 struct PersistMaps {
   CUtensorMap h[B200GRU_MAX_LAYERS][2];   // hidden buffers, box {64, 128}
   CUtensorMap whh[B200GRU_MAX_LAYERS];    // packed W_hh, box {64, 24}
   CUtensorMap wih[B200GRU_MAX_LAYERS];    // packed W_ih (layers >= 1)
-  CUtensorMap wfc;                        // W_fc, box {64, C}
+  CUtensorMap wfc;                        // W_fc, box {64, C/2}: each CTA of an FC pair takes half
 };
 
 struct PersistArgs {
@@ -77,7 +78,7 @@ struct PersistArgs {
   __nv_bfloat16 *h[B200GRU_MAX_LAYERS][2];   // [bpad, H] ping-pong
   const __nv_bfloat16 *t0p;                  // [P][C][3: n,r,z][16]
   uint32_t *cnt_h;       // [L][2][mt_max]  CTAs that have stored their slice of (layer, buffer, 128-name tile)
-  uint32_t *cnt_c;       // [mt_max]        steps whose characters are sampled for the tile
+  uint32_t *cnt_c;       // [mt_max]        2 x steps whose characters are sampled for the tile (one bump per FC CTA)
   int32_t *live;         // [T][mt_max]     names of the tile still running after step t
   uint32_t *done_cnt;    // FC CTAs that have finished the call
   const float *b_fc;
@@ -90,7 +91,34 @@ struct PersistArgs {
   uint32_t done_value;
   const uint32_t *ready_flag;
   uint32_t ready_value;
+  // optional in-kernel timeline (b200gru_model_persist_timeline): globaltimer
+  // stamps of the first weight CTA and the first FC CTA, per role
+  unsigned long long *timeline;
+  int timeline_fc_rank;  // which CTA of the first FC pair is instrumented (B200GRU_TL_FC_RANK)
 };
+
+// ---- timeline: [cta: 0 = first weight CTA, 1 = first FC CTA][role: 0 producer, 1 MMA, 2 epilogue][PS_TL_EVENTS]
+constexpr int PS_TL_EVENTS = 256;
+struct Timeline {
+  unsigned long long *p;
+  int i;
+  __device__ __forceinline__ void stamp(uint32_t code) {
+    if (p && i < PS_TL_EVENTS) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      p[i++] = (t << 16) | (code & 0xffffu);
+    }
+  }
+};
+__device__ __forceinline__ Timeline timeline_for(const unsigned long long *base, int cta, int role, bool on) {
+  Timeline t;
+  t.p = (base && on) ? const_cast<unsigned long long *>(base) + ((size_t)cta * 3 + role) * PS_TL_EVENTS : nullptr;
+  t.i = 0;
+  return t;
+}
+// event codes: (step << 8) | (layer << 4) | what
+enum { TL_WAIT_DONE = 1, TL_LOADS_ISSUED = 2, TL_MMA_START = 3, TL_MMA_ISSUED = 4, TL_ACC_READY = 5,
+       TL_PUBLISHED = 6, TL_CHARS_READY = 7, TL_START = 8, TL_WEIGHTS = 9 };
 
 // All lanes poll one address (one request); every lane has then acquired.
 // A cooperative kernel whose CTAs wait on each other must never hang the GPU on
@@ -105,7 +133,7 @@ __device__ __noinline__ void wait_timed_out(const uint32_t *p, uint32_t expect, 
 __device__ __forceinline__ void wait_counter_gpu(const uint32_t *p, uint32_t expect) {
   uint32_t polls = 0, v;
   while ((int32_t)((v = ld_acquire_gpu(p)) - expect) < 0) {
-    __nanosleep(kSpinNs);
+    if (kSpinNs) __nanosleep(kSpinNs);
     if (++polls == kWatchdogPolls) wait_timed_out(p, expect, v);
   }
 }
@@ -122,7 +150,7 @@ __device__ __forceinline__ bool pair_tile_dead(const PersistArgs &a, int step, i
   for (int r = 0; r < 2; ++r) {
     const int mt = m2 * 2 + r;
     if (mt >= a.m_tiles) continue;  // padding rows only
-    wait_counter_gpu(a.cnt_c + mt, (uint32_t)(step - 1));  // already true; orders the read below
+    wait_counter_gpu(a.cnt_c + mt, 2u * (uint32_t)(step - 1));  // already true; orders the read below
     dead = dead && (__ldcg(a.live + (size_t)(step - 2) * a.mt_max + mt) == 0);
   }
   return dead;
@@ -146,17 +174,18 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
   uint64_t *bars = reinterpret_cast<uint64_t *>(ring + (size_t)S * PS_A_BYTES);
   uint64_t *full_bar = bars;                         // [S]  (leader's is used)
   uint64_t *empty_bar = bars + PS_MAX_STAGES;        // [S]  (each CTA its own)
-  uint64_t *tmem_full = bars + 2 * PS_MAX_STAGES;    // [2]  (each CTA its own)
-  uint64_t *tmem_empty = bars + 2 * PS_MAX_STAGES + 2;  // [2] (leader's is used)
-  uint64_t *wbar = bars + 2 * PS_MAX_STAGES + 4;     // resident weights landed (leader's is used)
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * PS_MAX_STAGES + 5);
+  uint64_t *tmem_full = bars + 2 * PS_MAX_STAGES;    // [PS_ACC_STAGES]  (each CTA its own)
+  uint64_t *tmem_empty = tmem_full + PS_ACC_STAGES;  // [PS_ACC_STAGES]  (leader's is used)
+  uint64_t *wbar = tmem_empty + PS_ACC_STAGES;       // resident weights landed (leader's is used)
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(wbar + 1);
+  const bool tl_on = blockIdx.x == 0;
 
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < PS_ACC_STAGES; ++i) {
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], 2 * PS_EPI_WARPS);  // epilogue warps of both CTAs
     }
@@ -170,18 +199,20 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // Columns 16..63 ([r | z | n_h]) of a stage are zero whenever the stage is in
-  // the MMA warp's hands: the recurrent MMAs only ever accumulate.
+  // Every column of a stage is zero whenever the stage is in the MMA warp's
+  // hands, so every MMA simply accumulates and the two halves of a tile (own
+  // previous state first, the layer below's fresh state last) can come in the
+  // order their operands become available.
   if (warp >= 4) {
     const uint32_t lane_base0 = (uint32_t)((warp & 3) * 32) << 16;
     const int half0 = (warp - 4) >> 2;
     uint32_t zero[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) zero[i] = 0u;
+#pragma unroll 1
+    for (int st = 0; st < PS_ACC_STAGES; ++st)
 #pragma unroll
-    for (int st = 0; st < 2; ++st)
-#pragma unroll
-      for (int g = 1; g < 4; ++g)
+      for (int g = 0; g < 4; ++g)
         tmem_st8(tmem_base + lane_base0 + st * PS_ACC_COLS + g * 16 + half0 * 8, zero);
     tmem_st_wait();
   }
@@ -206,6 +237,8 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
       }
     }
     __syncwarp();
+    Timeline tl = timeline_for(a.timeline, 0, 0, tl_on && lane == 0);
+    tl.stamp(TL_START);
     int stage = 0;
     uint32_t phase = 0;
     for (int step = 0; step < a.T; ++step) {
@@ -214,13 +247,15 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
         for (int m2 = 0; m2 < a.m2_tiles; ++m2) {
           if (pair_tile_dead(a, step, m2)) continue;
           const int mt = m2 * 2 + (int)rank;
-          for (int part = 0; part < 2; ++part) {
-            // part 0: x = the layer below's fresh state; part 1: own previous state
+          for (int part = 1; part >= 0; --part) {
+            // part 1: own previous state (ready since the last step) first;
+            // part 0: x = the layer below's fresh state, the operand on the critical path
             if (part == 0 ? (l == 0) : (step == 0)) continue;
             const int src_l = part == 0 ? l - 1 : l;
             const int src_b = part == 0 ? wr : rd;
             const uint32_t rounds = part == 0 ? (uint32_t)(step / 2 + 1) : (uint32_t)((step - 1) / 2 + 1);
             wait_counter_gpu(a.cnt_h + ((size_t)src_l * 2 + src_b) * a.mt_max + mt, rounds * (uint32_t)a.P);
+            tl.stamp((step << 8) | (l << 4) | TL_WAIT_DONE);
             const CUtensorMap *map = &maps.h[src_l][src_b];
             for (int kb = 0; kb < kbH; ++kb) {
               mbar_wait_relaxed(&empty_bar[stage], phase ^ 1, 20);
@@ -233,6 +268,7 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
               __syncwarp();
               if (++stage == S) { stage = 0; phase ^= 1; }
             }
+            tl.stamp((step << 8) | (l << 4) | TL_LOADS_ISSUED);
           }
         }
     }
@@ -244,14 +280,17 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
       const uint32_t idesc = umma_idesc_bf16(2 * kTileM, PS_N);
       const uint64_t desc_ring = umma_desc_sw128(smem_u32(ring));
       const uint64_t desc_w = umma_desc_sw128(smem_u32(wsm));
+      Timeline tl = timeline_for(a.timeline, 0, 1, tl_on && lane == 0);
+      tl.stamp(TL_START);
       mbar_wait(wbar, 0);
       tc_fence_after();
+      tl.stamp(TL_WEIGHTS);
       for (int step = 0; step < a.T; ++step)
         for (int l = 0; l < a.L; ++l)
           for (int m2 = 0; m2 < a.m2_tiles; ++m2) {
             if (pair_tile_dead(a, step, m2)) continue;
-            const int kb_x = l > 0 ? kbH : 0;
-            const int kb_total = kb_x + (step > 0 ? kbH : 0);
+            const int kb_h = step > 0 ? kbH : 0;      // own previous state comes first
+            const int kb_total = kb_h + (l > 0 ? kbH : 0);
             if (kb_total == 0) continue;  // layer 0, step 0: the table row is everything
             mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
             tc_fence_after();
@@ -259,20 +298,21 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
             for (int kb = 0; kb < kb_total; ++kb) {
               mbar_wait(&full_bar[stage], phase);
               tc_fence_after();
+              if (kb == 0) tl.stamp((step << 8) | (l << 4) | TL_MMA_START);
               if (elect_one()) {
                 const uint64_t da = desc_ring + (uint64_t)((stage * PS_A_BYTES) >> 4);
-                if (kb < kb_x) {  // [n_i | r | z] <- x . W_ih^T ; the tile's first MMA overwrites
-                  const uint64_t db = desc_w + (uint64_t)((a.off_ih[l] + kb * PS_KB_BYTES) >> 4);
-                  umma_bf16_2sm(d, da, db, idesc, kb != 0 ? 1u : 0u);
-                  umma_bf16_2sm(d, da + 2, db + 2, idesc, 1u);
-                  umma_bf16_2sm(d, da + 4, db + 4, idesc, 1u);
-                  umma_bf16_2sm(d, da + 6, db + 6, idesc, 1u);
-                } else {          // [r | z | n_h] += h . W_hh^T
-                  const uint64_t db = desc_w + (uint64_t)((a.off_hh[l] + (kb - kb_x) * PS_KB_BYTES) >> 4);
+                if (kb < kb_h) {  // [r | z | n_h] += h . W_hh^T
+                  const uint64_t db = desc_w + (uint64_t)((a.off_hh[l] + kb * PS_KB_BYTES) >> 4);
                   umma_bf16_2sm(d + 16, da, db, idesc, 1u);
                   umma_bf16_2sm(d + 16, da + 2, db + 2, idesc, 1u);
                   umma_bf16_2sm(d + 16, da + 4, db + 4, idesc, 1u);
                   umma_bf16_2sm(d + 16, da + 6, db + 6, idesc, 1u);
+                } else {          // [n_i | r | z] += x . W_ih^T
+                  const uint64_t db = desc_w + (uint64_t)((a.off_ih[l] + (kb - kb_h) * PS_KB_BYTES) >> 4);
+                  umma_bf16_2sm(d, da, db, idesc, 1u);
+                  umma_bf16_2sm(d, da + 2, db + 2, idesc, 1u);
+                  umma_bf16_2sm(d, da + 4, db + 4, idesc, 1u);
+                  umma_bf16_2sm(d, da + 6, db + 6, idesc, 1u);
                 }
                 umma_commit_2sm(&empty_bar[stage], 0b11);
                 if (kb == kb_total - 1) umma_commit_2sm(&tmem_full[acc_stage], 0b11);
@@ -280,7 +320,8 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
               __syncwarp();
               if (++stage == S) { stage = 0; phase ^= 1; }
             }
-            if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+            tl.stamp((step << 8) | (l << 4) | TL_MMA_ISSUED);
+            if (++acc_stage == PS_ACC_STAGES) { acc_stage = 0; acc_phase ^= 1; }
           }
     }
   } else if (warp >= 4) {
@@ -292,6 +333,8 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     const int unit0 = pair * PS_UNITS + half * 8;     // first of this thread's hidden units
     const int etid = threadIdx.x - 128;
+    Timeline tl = timeline_for(a.timeline, 0, 2, tl_on && etid == 0);
+    tl.stamp(TL_START);
     int acc_stage = 0;
     uint32_t acc_phase = 0;
     for (int step = 0; step < a.T; ++step) {
@@ -325,7 +368,8 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
             // current character (embedding + 3 matvecs + biases, ref:669-733)
             int c = a.sos;  // ref:652
             if (step > 0 && mt < a.m_tiles) {
-              wait_counter_gpu(a.cnt_c + mt, (uint32_t)step);  // characters of step-1 are sampled
+              wait_counter_gpu(a.cnt_c + mt, 2u * (uint32_t)step);  // characters of step-1 are sampled (both FC CTAs)
+              tl.stamp((step << 8) | (l << 4) | TL_CHARS_READY);
               if (row < a.n) c = __ldcg(a.chars + row);
             }
             const uint4 *trow = reinterpret_cast<const uint4 *>(
@@ -342,26 +386,15 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
           }
           uint32_t vn[8], vr[8], vz[8], vh[8];
           if (has_mma) {
-            mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, 40);
+            mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, 20);
             tc_fence_after();
+            tl.stamp((step << 8) | (l << 4) | TL_ACC_READY);
             const uint32_t t = tmem_base + lane_base + acc_stage * PS_ACC_COLS + half * 8;
             if (l > 0) tmem_ld8(t, vn);
             tmem_ld8(t + 16, vr);
             tmem_ld8(t + 32, vz);
             tmem_ld8(t + 48, vh);
             tmem_ld_wait();
-            // hand the stage back with [r | z | n_h] zeroed
-            uint32_t zero[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) zero[i] = 0u;
-            tmem_st8(t + 16, zero);
-            tmem_st8(t + 32, zero);
-            tmem_st8(t + 48, zero);
-            tmem_st_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
-            if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
           } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) vr[i] = vz[i] = vh[i] = 0u;
@@ -396,8 +429,27 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
           // publish: this CTA's slice of (layer, buffer, tile) is in place
           named_bar_sync(PS_EPI_BAR, PS_EPI_WARPS * 32);
           if (etid == 0) {
-            __threadfence();
+            // the barrier above orders every epilogue thread's stores before this
+            // release (cumulativity), which publishes them at GPU scope
             red_release_gpu_add(a.cnt_h + ((size_t)l * 2 + wr) * a.mt_max + mt, 1u);
+            tl.stamp((step << 8) | (l << 4) | TL_PUBLISHED);
+          }
+          if (has_mma) {
+            // only now (off the critical path: the MMA warp has seven more
+            // stages) hand the accumulator stage back, zeroed
+            const uint32_t t = tmem_base + lane_base + acc_stage * PS_ACC_COLS + half * 8;
+            uint32_t zero[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) zero[i] = 0u;
+            if (l > 0) tmem_st8(t, zero);
+            tmem_st8(t + 16, zero);
+            tmem_st8(t + 32, zero);
+            tmem_st8(t + 48, zero);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
+            if (++acc_stage == PS_ACC_STAGES) { acc_stage = 0; acc_phase ^= 1; }
           }
         }
     }
@@ -412,57 +464,78 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
 }
 
 // ----------------------------------------------------------------- FC CTAs
+// FC + softmax + sampling (ref:858-878) for one 128-name tile per CTA PAIR.
+// The two CTAs split the alphabet: CTA c computes logits of characters
+// [c*C/2, (c+1)*C/2) (UMMA M = 128, N = C/2), so the GEMM on the critical path of
+// every character takes half as long as on one CTA.  Inside a CTA two threads
+// share a name, so a name's probabilities live in four segments.  Softmax needs
+// one exchange: every thread publishes the sum of its segment's exponentials to
+// both CTAs (distributed shared memory + an mbarrier that collects the warps of
+// both CTAs); with the four sums every thread knows the total and where its own
+// segment starts in the CDF, hence which segment contains the sampled point —
+// only that segment's thread walks, 16 columns at most, and does the name's
+// bookkeeping.
+constexpr int PS_FC_STAGE_BYTES = PS_A_BYTES + 128 * 128;   // A tile + up to 128 rows of W_fc
+constexpr int PS_FC_TMEM_COLS = 256;                          // two accumulator stages of <= 128 columns
+
 __device__ __forceinline__ void persist_fc(const PersistMaps &maps, const PersistArgs &a, uint8_t *smem) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int C = a.C, L = a.L;
-  const int f = (int)blockIdx.x - 2 * a.P;
-  const uint32_t b_bytes = (uint32_t)C * 128u;
-  const int stage_bytes = PS_A_BYTES + 256 * 128;
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + PS_FC_STAGES * stage_bytes);
+  const uint32_t rank = cluster_ctarank();                 // which half of the alphabet
+  const int fp = ((int)blockIdx.x - 2 * a.P) >> 1;         // FC pair index
+  const int n_fcp = a.n_fc >> 1;
+  const int Nh = C >> 1;
+  const uint32_t b_bytes = (uint32_t)Nh * 128u;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + PS_FC_STAGES * PS_FC_STAGE_BYTES);
   uint64_t *full_bar = bars, *empty_bar = bars + PS_FC_STAGES;
-  uint64_t *tmem_full = bars + 2 * PS_FC_STAGES, *tmem_empty = bars + 2 * PS_FC_STAGES + 2;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * PS_FC_STAGES + 4);
-  int *live_cnt = reinterpret_cast<int *>(bars + 2 * PS_FC_STAGES + 5);
-  float *part_sum = reinterpret_cast<float *>(smem + PS_FC_STAGES * stage_bytes + 512);  // [2][128]
-  int *part_sel = reinterpret_cast<int *>(part_sum + 2 * kTileM);                        // [128]
+  uint64_t *tmem_full = bars + 2 * PS_FC_STAGES, *tmem_empty = tmem_full + 2;
+  uint64_t *xbar = tmem_empty + 2;                         // segment sums of both CTAs are in place
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(xbar + 1);
+  float *seg_sum = reinterpret_cast<float *>(smem + PS_FC_STAGES * PS_FC_STAGE_BYTES + 512);  // [2][4][128]
 
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < PS_FC_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], PS_EPI_WARPS); }
-    *live_cnt = 0;
+    mbar_init(xbar, 2 * PS_EPI_WARPS);                     // epilogue warps of both CTAs
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  cluster_sync_all();                                       // the partner's barriers exist before we signal them
+  if (warp == 2) tmem_alloc<PS_FC_TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // A tile of this CTA is skipped (no GEMM, no sampling) once it reported no
-  // running names; every role reads that from the same global word.
+  // A tile is skipped (no GEMM, no sampling) once it reported no running names;
+  // every role of both CTAs reads that from the same global word.  cnt_c counts
+  // two publications per step (one per CTA of the pair).
   auto tile_dead = [&](int step, int mt) -> bool {
     if (step == 0) return false;
-    wait_counter_gpu(a.cnt_c + mt, (uint32_t)step);  // our own epilogue of step-1 has published
+    wait_counter_gpu(a.cnt_c + mt, 2u * (uint32_t)step);
     return __ldcg(a.live + (size_t)(step - 1) * a.mt_max + mt) == 0;
   };
+  const bool tl_on = fp == 0 && (int)rank == a.timeline_fc_rank;
 
   if (warp == 0) {
+    Timeline tl = timeline_for(a.timeline, 1, 0, tl_on && lane == 0);
+    tl.stamp(TL_START);
     int stage = 0;
     uint32_t phase = 0;
     for (int step = 0; step < a.T; ++step) {
       const int wr = (step & 1) ^ 1;
-      for (int mt = f; mt < a.m_tiles; mt += a.n_fc) {
+      for (int mt = fp; mt < a.m_tiles; mt += n_fcp) {
         if (tile_dead(step, mt)) continue;
         wait_counter_gpu(a.cnt_h + ((size_t)(L - 1) * 2 + wr) * a.mt_max + mt,
                          (uint32_t)(step / 2 + 1) * (uint32_t)a.P);
+        tl.stamp((step << 8) | TL_WAIT_DONE);
         for (int kb = 0; kb < a.kbH; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (elect_one()) {
-            uint8_t *sa = smem + stage * stage_bytes;
+            uint8_t *sa = smem + stage * PS_FC_STAGE_BYTES;
             if (kb == 0) fence_proxy_async();
             mbar_expect_tx(&full_bar[stage], PS_A_BYTES + b_bytes);
             tma_load_2d(sa, &maps.h[L - 1][wr], &full_bar[stage], kb * 64, mt * kTileM);
-            tma_load_2d(sa + PS_A_BYTES, &maps.wfc, &full_bar[stage], kb * 64, 0);
+            tma_load_2d(sa + PS_A_BYTES, &maps.wfc, &full_bar[stage], kb * 64, (int)rank * Nh);
           }
           __syncwarp();
           if (++stage == PS_FC_STAGES) { stage = 0; phase ^= 1; }
@@ -472,19 +545,22 @@ __device__ __forceinline__ void persist_fc(const PersistMaps &maps, const Persis
   } else if (warp == 1) {
     int stage = 0, acc_stage = 0;
     uint32_t phase = 0, acc_phase = 0;
-    const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)C);
+    const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)Nh);
     const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
+    Timeline tl = timeline_for(a.timeline, 1, 1, tl_on && lane == 0);
+    tl.stamp(TL_START);
     for (int step = 0; step < a.T; ++step)
-      for (int mt = f; mt < a.m_tiles; mt += a.n_fc) {
+      for (int mt = fp; mt < a.m_tiles; mt += n_fcp) {
         if (tile_dead(step, mt)) continue;
         mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d = tmem_base + acc_stage * 256;
+        const uint32_t d = tmem_base + acc_stage * 128;
         for (int kb = 0; kb < a.kbH; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+          if (kb == 0) tl.stamp((step << 8) | TL_MMA_START);
           if (elect_one()) {
-            const uint64_t da = desc0 + (uint64_t)((stage * stage_bytes) >> 4);
+            const uint64_t da = desc0 + (uint64_t)((stage * PS_FC_STAGE_BYTES) >> 4);
             const uint64_t db = da + (uint64_t)(PS_A_BYTES >> 4);
             umma_bf16(d, da, db, idesc, kb != 0 ? 1u : 0u);
             umma_bf16(d, da + 2, db + 2, idesc, 1u);
@@ -496,20 +572,26 @@ __device__ __forceinline__ void persist_fc(const PersistMaps &maps, const Persis
           __syncwarp();
           if (++stage == PS_FC_STAGES) { stage = 0; phase ^= 1; }
         }
+        tl.stamp((step << 8) | TL_MMA_ISSUED);
         if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
       }
   } else if (warp >= 4) {
-    // Two threads per name (same TMEM lane): half 0 owns columns [0, split),
-    // half 1 owns [split, C); see fc_sample_kernel in gru_tc_sm100.cu.
     const int quarter = warp & 3;
     const int half = (warp - 4) >> 2;
-    const int rl = quarter * 32 + lane;
+    const int rl = quarter * 32 + lane;                    // row within the tile
     const int etid = threadIdx.x - 128;
-    const int split = ((C / 16 + 1) / 2) * 16;
-    const int cbeg = half == 0 ? 0 : split, cend = half == 0 ? split : C;
+    const int seg = 2 * (int)rank + half;                  // this thread's segment of the alphabet (in CDF order)
+    const int split = ((Nh / 16 + 1) / 2) * 16;
+    const int cbeg = half == 0 ? 0 : split, cend = half == 0 ? split : Nh;   // columns of this CTA's accumulator
+    const int col0 = (int)rank * Nh;                       // character id of accumulator column 0
+    const uint32_t seg_remote = mapa_u32(seg_sum, rank ^ 1u);
+    const uint32_t xbar_remote = mapa_u32(xbar, rank ^ 1u);
+    const uint32_t xbar_local = mapa_u32(xbar, rank);
     int acc_stage = 0;
     uint32_t acc_phase = 0;
     const float kLog2e = 1.4426950408889634f;
+    Timeline tl = timeline_for(a.timeline, 1, 2, tl_on && etid == 0);
+    tl.stamp(TL_START);
     if (a.ready_flag) {  // the root's upload of the random floats has landed (ref:636)
       uint32_t polls = 0, v;
       while ((int32_t)((v = ld_acquire_sys(a.ready_flag)) - a.ready_value) < 0) {
@@ -517,93 +599,128 @@ __device__ __forceinline__ void persist_fc(const PersistMaps &maps, const Persis
         if (++polls == 4 * kWatchdogPolls) wait_timed_out(a.ready_flag, a.ready_value, v);
       }
     }
+    int it = 0;
     for (int step = 0; step < a.T; ++step)
-      for (int mt = f; mt < a.m_tiles; mt += a.n_fc) {
+      for (int mt = fp; mt < a.m_tiles; mt += n_fcp) {
         if (tile_dead(step, mt)) {
-          if (etid == 0) {
-            a.live[(size_t)step * a.mt_max + mt] = 0;
-            __threadfence();
-            red_release_gpu_add(a.cnt_c + mt, 1u);
-          }
+          if (etid == 0) red_release_gpu_add(a.cnt_c + mt, 1u);  // live[step][mt] stays 0
           continue;
         }
         const int row = mt * kTileM + rl;
         const bool valid = row < a.n;
-        const bool live = valid && (step == 0 || a.alive[row] != 0);
+        const bool live = valid && (step == 0 || __ldcg(a.alive + row) != 0);
+        // this step's random float: fetched (over NVLink from the root rank's
+        // buffer when data parallel, ref:636) long before it is needed
         const float r = live ? a.rfloats[(size_t)row * a.T + step] : 2.0f;
-        mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, 40);
+        mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, 20);
         tc_fence_after();
-        const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * 256;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll 1
-        for (int c0 = cbeg; c0 < cend; c0 += 16) {
-          uint32_t v[16];
-          tmem_ld16(t + c0, v);
-          tmem_ld_wait();
+        tl.stamp((step << 8) | TL_ACC_READY);
+        const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * 128;
+        // pass 1: e_i = exp(f_i + b_i) kept in TMEM in place; one sum per 16 columns
+        float cs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float4 b = __ldg(reinterpret_cast<const float4 *>(a.b_fc + c0) + q);
-            const float bb[4] = {b.x, b.y, b.z, b.w};
-            float e[4];
+        for (int k = 0; k < 4; ++k) {
+          const int c0 = cbeg + 16 * k;
+          if (c0 < cend) {
+            uint32_t v[16];
+            tmem_ld16(t + c0, v);
+            tmem_ld_wait();
+            float e[16];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float x = __uint_as_float(v[q * 4 + j]) + bb[j];
-              if (a.logits && valid) a.logits[(size_t)row * C + c0 + q * 4 + j] = live ? x : 0.0f;
-              e[j] = ex2_approx(x * kLog2e);
-              v[q * 4 + j] = __float_as_uint(e[j]);
+            for (int q = 0; q < 4; ++q) {
+              const float4 b = __ldg(reinterpret_cast<const float4 *>(a.b_fc + col0 + c0) + q);
+              const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float x = __uint_as_float(v[q * 4 + j]) + bb[j];
+                if (a.logits && valid) a.logits[(size_t)row * C + col0 + c0 + q * 4 + j] = live ? x : 0.0f;
+                e[q * 4 + j] = ex2_approx(x * kLog2e);
+                v[q * 4 + j] = __float_as_uint(e[q * 4 + j]);
+              }
             }
-            s0 += e[0]; s1 += e[1]; s2 += e[2]; s3 += e[3];
+            tmem_st16(t + c0, v);
+            cs[k] = (((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]))) +
+                    (((e[8] + e[9]) + (e[10] + e[11])) + ((e[12] + e[13]) + (e[14] + e[15])));
           }
-          tmem_st16(t + c0, v);
         }
         tmem_st_wait();
-        part_sum[half * kTileM + rl] = (s0 + s1) + (s2 + s3);
-        named_bar_sync(PS_EPI_BAR, PS_EPI_WARPS * 32);
-        const float sum_lo = part_sum[rl], sum = sum_lo + part_sum[kTileM + rl];
-        const float inv = 1.0f / sum;
-        float psum = half == 0 ? 0.0f : sum_lo * inv;
-        int sel = -1;
-#pragma unroll 1
-        for (int c0 = cbeg; c0 < cend; c0 += 16) {
-          if (__all_sync(0xffffffffu, sel >= 0 || !live)) break;
-          uint32_t v[16];
-          tmem_ld16(t + c0, v);
-          tmem_ld_wait();
+        tl.stamp((step << 8) | 10);
+        // exchange: this segment's mass to both CTAs
+        float *mine_sums = seg_sum + (size_t)(it & 1) * 4 * kTileM;
+        const float my_sum = ((cs[0] + cs[1]) + cs[2]) + cs[3];
+        mine_sums[seg * kTileM + rl] = my_sum;
+        st_shared_cluster_f32(seg_remote + (uint32_t)(((it & 1) * 4 + seg) * kTileM + rl) * 4u, my_sum);
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive_cluster(xbar_local);
+          mbar_arrive_cluster(xbar_remote);
+        }
+        mbar_wait_cluster(xbar, (uint32_t)it & 1u);
+        tl.stamp((step << 8) | 11);
+        const float S0 = mine_sums[rl], S1 = mine_sums[kTileM + rl], S2 = mine_sums[2 * kTileM + rl],
+                    S3 = mine_sums[3 * kTileM + rl];
+        const float P1 = S0, P2 = P1 + S1, P3 = P2 + S2, tot = P3 + S3;
+        // first i with sum_{j<=i} e_j > r * sum (ref:322-333 on unnormalised mass);
+        // if the mass never exceeds it the last character wins (ref:332)
+        const float rs = r * tot;
+        const bool fallback = !(tot > rs);
+        const int owner = fallback ? 3 : (P1 > rs ? 0 : (P2 > rs ? 1 : (P3 > rs ? 2 : 3)));
+        const bool mine = live && owner == seg;
+        int sel = (mine && fallback) ? C - 1 : -1;
+        float p = seg == 0 ? 0.0f : (seg == 1 ? P1 : (seg == 2 ? P2 : P3));
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            psum = fmaf(__uint_as_float(v[i]), inv, psum);
-            if (sel < 0 && psum > r) sel = c0 + i;
+        for (int k = 0; k < 4; ++k) {
+          const int c0 = cbeg + 16 * k;
+          if (c0 < cend) {
+            const bool need = mine && sel < 0 && (p + cs[k] > rs);
+            if (__any_sync(0xffffffffu, need)) {      // tcgen05.ld is warp-collective
+              uint32_t v[16];
+              tmem_ld16(t + c0, v);
+              tmem_ld_wait();
+              if (need) {
+                float q = p;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  q += __uint_as_float(v[i]);
+                  if (sel < 0 && q > rs) sel = col0 + c0 + i;
+                }
+                if (sel < 0) sel = col0 + c0 + 15;      // tree sum crossed, running sum did not (rounding)
+              }
+            }
+            p += cs[k];
           }
         }
+        if (mine && sel < 0) sel = col0 + cend - 1;
+        tl.stamp((step << 8) | 12);
+        // accumulator drained: hand the TMEM stage back before the bookkeeping
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
-        if (half == 1) part_sel[rl] = sel;
-        named_bar_sync(PS_EPI_BAR, PS_EPI_WARPS * 32);
         bool still = false;
-        if (half == 0 && valid) {
-          if (sel < 0) sel = part_sel[rl];
-          if (sel < 0) sel = C - 1;               // ref:332
-          char *orow = a.output + (size_t)row * (a.T + 1);
-          if (step == 0)
-            for (int l = 1; l <= a.T; ++l) orow[l] = 0;  // ref:643
-          if (live) {
-            orow[step] = (char)sel;               // ref:877
-            a.chars[row] = sel;
-            still = sel != a.eos;                 // ref:881
-            a.alive[row] = still ? 1 : 0;
+        char *orow = a.output + (size_t)row * (a.T + 1);
+        if (mine) {
+          a.chars[row] = sel;
+          still = sel != a.eos;                     // ref:881
+          a.alive[row] = still ? 1 : 0;
+          if (step == 0) {                          // first byte + NUL padding, ref:643
+            orow[0] = (char)sel;
+            for (int l = 1; l <= a.T; ++l) orow[l] = 0;
           }
         }
         const unsigned running = __ballot_sync(0xffffffffu, still);
-        if (half == 0 && lane == 0 && running) atomicAdd(live_cnt, __popc(running));
+        if (lane == 0 && running) atomicAdd(a.live + (size_t)step * a.mt_max + mt, __popc(running));
         named_bar_sync(PS_EPI_BAR, PS_EPI_WARPS * 32);
+        tl.stamp((step << 8) | 13);
         if (etid == 0) {
-          a.live[(size_t)step * a.mt_max + mt] = *live_cnt;
-          *live_cnt = 0;
-          __threadfence();
-          red_release_gpu_add(a.cnt_c + mt, 1u);   // this tile's characters of `step` are in place
+          red_release_gpu_add(a.cnt_c + mt, 1u);   // this CTA's share of the tile's characters is in place
+          tl.stamp((step << 8) | TL_PUBLISHED);
         }
+        // the output byte (possibly a store over NVLink into the root's row,
+        // ref:877, :889) is not needed by the next step: it goes out after the
+        // publication so the release above does not wait for it
+        if (mine && step > 0) orow[step] = (char)sel;
         if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+        ++it;
       }
     // completion: rows of every FC CTA are written before the flag is (ref:889)
     named_bar_sync(PS_EPI_BAR, PS_EPI_WARPS * 32);
@@ -616,10 +733,10 @@ __device__ __forceinline__ void persist_fc(const PersistMaps &maps, const Persis
     }
   }
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();   // the partner may still be writing our seg_sum / signalling our xbar
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
+    tmem_dealloc<PS_FC_TMEM_COLS>(tmem_base);
   }
 }
 
@@ -690,7 +807,8 @@ int persist_prepare(b200gru_model *m) {
   const b200gru_config &c = m->cfg;
   const int H = c.hidden, C = c.num_char, L = c.num_layers;
   m->ps_ok = false;
-  if (!m->tc_ok || m->tp_world != 1 || H % 64 != 0 || m->pw_log2 != 0 && (1 << m->pw_log2) != H) return 0;
+  // needs: row-major hidden buffers (H a power of two), an alphabet the FC pair can halve
+  if (!m->tc_ok || m->tp_world != 1 || H % 64 != 0 || (1 << m->pw_log2) != H || C % 32 != 0) return 0;
   int sms = 148, coop = 0, max_smem = 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, m->device);
   cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, m->device);
@@ -698,7 +816,7 @@ int persist_prepare(b200gru_model *m) {
   const int P = H / PS_UNITS;
   const int kbH = H / 64;
   const size_t w_bytes = (size_t)(2 * L - 1) * kbH * PS_KB_BYTES;
-  const size_t fc_bytes = 1024 + (size_t)PS_FC_STAGES * (PS_A_BYTES + 256 * 128) + 4096;
+  const size_t fc_bytes = 1024 + (size_t)PS_FC_STAGES * PS_FC_STAGE_BYTES + 512 + 4096;
   int stages = (int)(((size_t)max_smem - 1024 - 1024 - w_bytes) / PS_A_BYTES);
   if ((size_t)max_smem < 1024 + 1024 + w_bytes + 2 * PS_A_BYTES) stages = 0;
   if (stages > PS_MAX_STAGES) stages = PS_MAX_STAGES;
@@ -726,6 +844,7 @@ int persist_prepare(b200gru_model *m) {
   if (int rc = ps_alloc(m, &m->ps_t0p, (size_t)3 * H * C)) return rc;
   pack_t0p_kernel<<<blocks((size_t)3 * H * C), TPB>>>(m->t0_raw, m->P(ix.b_i(0, 0)), m->P(ix.b_h(0, 0)),
                                                       m->ps_t0p, C, H);
+  if (int rc = make_tmap_bf16_2d(&m->ps_map_wfc_half, m->w_fc, (uint64_t)C, H, C / 2, 64, m->ldh)) return rc;
   if (int rc = ps_alloc(m, &m->ps_sync, ps_sync_words(m))) return rc;
   B200_CUDA(cudaMemset(m->ps_sync, 0, ps_sync_words(m) * sizeof(uint32_t)));
   B200_CUDA(cudaGetLastError());
@@ -769,7 +888,7 @@ int persist_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t
   a.mt_max = m->bpad / kTileM;
   a.T = c.max_len; a.L = L; a.H = H; a.C = c.num_char; a.kbH = H / 64;
   a.P = m->ps_pairs;
-  a.n_fc = a.m_tiles < m->ps_fc_max ? ((a.m_tiles + 1) & ~1) : m->ps_fc_max;
+  a.n_fc = 2 * a.m_tiles < m->ps_fc_max ? 2 * a.m_tiles : m->ps_fc_max;  // one CTA pair per 128-name tile
   a.stages = m->ps_stages;
   a.sos = c.sos; a.eos = c.eos;
   uint32_t off = 0;
@@ -785,7 +904,7 @@ int persist_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t
     if (l > 0) maps.wih[l] = m->ps_map_w_ih[l];
   }
   a.w_bytes = off;
-  maps.wfc = m->map_w_fc;
+  maps.wfc = m->ps_map_wfc_half;
   a.t0p = m->ps_t0p;
   a.cnt_h = m->ps_sync;
   a.cnt_c = a.cnt_h + (size_t)L * 2 * a.mt_max;
@@ -801,6 +920,15 @@ int persist_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t
   a.done_value = io->done_value;
   a.ready_flag = io->ready_flag;
   a.ready_value = io->ready_value;
+  a.timeline = nullptr;
+  a.timeline_fc_rank = 0;
+  if (m->trace_on) {
+    if (const char *e = getenv("B200GRU_TL_FC_RANK")) a.timeline_fc_rank = atoi(e) & 1;  // tracing also records the in-kernel timeline of two CTAs
+    if (!m->ps_timeline)
+      if (int rc = ps_alloc(m, &m->ps_timeline, (size_t)2 * 3 * PS_TL_EVENTS)) return rc;
+    B200_CUDA(cudaMemsetAsync(m->ps_timeline, 0, sizeof(unsigned long long) * 2 * 3 * PS_TL_EVENTS, s));
+    a.timeline = m->ps_timeline;
+  }
 
   m->trace_begin(s);
   if (io->ready_event) B200_CUDA(cudaStreamWaitEvent(s, static_cast<cudaEvent_t>(io->ready_event), 0));
@@ -826,3 +954,17 @@ int persist_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t
 }
 
 }  // namespace b200gru
+
+// In-kernel timeline of the last traced persistent generate: `out` receives
+// 2 x 3 x 256 words, [cta: first weight CTA, first FC CTA][role: TMA producer,
+// MMA issuer, epilogue][event]; each word is (globaltimer_ns << 16) | code with
+// code = (step << 8) | (layer << 4) | event, 0 = unused slot.
+extern "C" int b200gru_model_persist_timeline(b200gru_model *m, unsigned long long *out, int max_words) {
+  using namespace b200gru;
+  B200_REQUIRE(m && out, "null argument");
+  const int words = 2 * 3 * PS_TL_EVENTS;
+  B200_REQUIRE(max_words >= words, "buffer must hold %d words", words);
+  if (!m->ps_timeline) return 0;
+  B200_CUDA(cudaMemcpy(out, m->ps_timeline, sizeof(unsigned long long) * words, cudaMemcpyDeviceToHost));
+  return words;
+}

@@ -78,8 +78,10 @@ struct b200gru_model {
   __nv_bfloat16 *ps_w_ih[B200GRU_MAX_LAYERS] = {};   // packed [H/16][n|r|z x 16][H]
   __nv_bfloat16 *ps_w_hh[B200GRU_MAX_LAYERS] = {};   // packed [H/16][r|z|n x 16][H]
   CUtensorMap ps_map_w_ih[B200GRU_MAX_LAYERS], ps_map_w_hh[B200GRU_MAX_LAYERS];
+  CUtensorMap ps_map_wfc_half;       // W_fc with a box of C/2 rows (FC CTA pairs split the alphabet)
   __nv_bfloat16 *ps_t0p = nullptr;   // [H/16][C][n|r|z][16] folded layer-0 input table
   uint32_t *ps_sync = nullptr;       // per-tile counters + live counts, zeroed per call
+  unsigned long long *ps_timeline = nullptr;  // in-kernel globaltimer stamps (tracing only)
 
   // --- tensor parallelism over the hidden dimension (tp_world == 1: off)
   int tp_world = 1, tp_rank = 0;

@@ -150,6 +150,27 @@ class NameGenerator:
         n = _native.check(self._lib.b200gru_model_get_trace(self._h, ms, names, cap), "get_trace")
         return [(names[i].decode(), ms[i]) for i in range(n)]
 
+    def persist_timeline(self) -> dict:
+        """In-kernel timeline of the last traced persistent generate:
+        `{(cta, role): [(t_us, step, layer, event), ...]}` with cta in
+        ("weights0", "fc0"), role in ("tma", "mma", "epilogue"), times relative to
+        the first stamp.  Events are listed in include/b200gru.h."""
+        words = 2 * 3 * 256
+        buf = (ctypes.c_uint64 * words)()
+        n = _native.check(self._lib.b200gru_model_persist_timeline(self._h, buf, words), "persist_timeline")
+        vals = [v for v in buf[:n] if v]
+        if not vals:
+            return {}
+        t0 = min(v >> 16 for v in vals)
+        out = {}
+        for ci, cta in enumerate(("weights0", "fc0")):
+            for ri, role in enumerate(("tma", "mma", "epilogue")):
+                base = (ci * 3 + ri) * 256
+                ev = [((v >> 16) - t0) / 1e3 for v in buf[base:base + 256] if v]
+                codes = [v & 0xffff for v in buf[base:base + 256] if v]
+                out[(cta, role)] = [(t, c >> 8, (c >> 4) & 15, c & 15) for t, c in zip(ev, codes)]
+        return out
+
     def debug_logits(self, n: int) -> torch.Tensor:
         """Last step's pre-softmax FC outputs for the first `n` names."""
         out = torch.empty(n, self.cfg.num_char, dtype=torch.float32, device=torch.device("cuda", self.device))

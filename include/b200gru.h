@@ -189,6 +189,16 @@ int b200gru_model_set_trace(b200gru_model *m, int on);
 int b200gru_model_get_trace(b200gru_model *m, float *ms, const char **names,
                             int max_spans);
 
+/* Persistent path only: in-kernel timeline of the last generate run with
+ * set_trace(m, 1).  `out` receives 2 x 3 x 256 words, [cta: first weight CTA,
+ * first FC CTA][role: TMA producer, MMA issuer, epilogue][event]; a word is
+ * (globaltimer_ns << 16) | (step << 8) | (layer << 4) | event, 0 = unused.
+ * Events: 1 operand counter reached, 2 loads issued, 3 first operand landed,
+ * 4 MMAs issued, 5 accumulator ready, 6 result published, 7 characters of the
+ * previous step visible, 8 role started, 9 resident weights landed.
+ * Returns the number of words written (0: nothing recorded). */
+int b200gru_model_persist_timeline(b200gru_model *m, unsigned long long *out, int max_words);
+
 /* Kernel that spins (ld.acquire.sys) until flags[i] >= value (wrap-safe) for all i<n;
  * rank 0 runs it after its own generate to complete the gather. */
 int b200gru_wait_flags(const uint32_t *flags, int n, uint32_t value,
