@@ -181,6 +181,7 @@ int b200gru_model_destroy(b200gru_model *m) {
   for (auto &g : m->graphs) {
     cudaGraphExecDestroy(g.exec);
     if (g.exec_tail) cudaGraphExecDestroy(g.exec_tail);
+    if (g.graph) cudaGraphDestroy(g.graph);
   }
   if (m->cap_stream) cudaStreamDestroy(m->cap_stream);
   for (void *p : m->allocs) {
@@ -243,13 +244,35 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
     // Replay a captured graph when nothing about the call varies: no
     // completion flag (its value changes per call), no tensor-parallel
     // counters, no tracing.
-    const bool graphable = m->use_graph && m->tp_world == 1 && !io->done_flag && !io->ready_flag &&
-                           !m->trace_on;
+    // Replayable: no tensor-parallel counters, no tracing.  Data-parallel flags
+    // are fine: their addresses are part of the cache key and the per-call epoch
+    // values are patched into the two kernel nodes that carry them.
+    const bool graphable = m->use_graph && m->tp_world == 1 && !m->trace_on &&
+                           !(io->ready_event && (io->done_flag || io->ready_flag));
     if (!graphable) return tc_generate(m, n, io, s);
     const bool split = io->ready_event != nullptr;  // two graphs with an event wait in between
     auto launch = [&](b200gru_model::GraphEntry &g) -> int {
       g.last_use = ++m->graph_clock;
       m->last_launches = g.launches;
+      if (g.ready_node) {
+        const uint32_t *flags = io->ready_flag;
+        int cnt = 1;
+        uint32_t value = io->ready_value;
+        void *args[3] = {&flags, &cnt, &value};
+        cudaKernelNodeParams p{};
+        p.func = reinterpret_cast<void *>(wait_flags_kernel);
+        p.gridDim = dim3(1); p.blockDim = dim3(32); p.kernelParams = args;
+        B200_CUDA(cudaGraphExecKernelNodeSetParams(g.exec, g.ready_node, &p));
+      }
+      if (g.done_node) {
+        uint32_t *flag = io->done_flag;
+        uint32_t value = io->done_value;
+        void *args[2] = {&flag, &value};
+        cudaKernelNodeParams p{};
+        p.func = reinterpret_cast<void *>(tc_signal_done_kernel);
+        p.gridDim = dim3(1); p.blockDim = dim3(1); p.kernelParams = args;
+        B200_CUDA(cudaGraphExecKernelNodeSetParams(g.exec, g.done_node, &p));
+      }
       B200_CUDA(cudaGraphLaunch(g.exec, s));
       if (g.exec_tail) {
         B200_CUDA(cudaStreamWaitEvent(s, static_cast<cudaEvent_t>(io->ready_event), 0));
@@ -259,7 +282,8 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
     };
     for (auto &g : m->graphs)
       if (g.n == n && g.rfloats == io->rfloats && g.output == io->output &&
-          g.logits == m->debug_logits && (g.exec_tail != nullptr) == split)
+          g.logits == m->debug_logits && (g.exec_tail != nullptr) == split &&
+          g.done_flag == io->done_flag && g.ready_flag == io->ready_flag)
         return launch(g);
     // Capture on a private stream (the caller's may be the legacy default
     // stream, which cannot be captured); the graph is launched on the caller's.
@@ -271,11 +295,32 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
       B200_CUDA(cudaStreamBeginCapture(m->cap_stream, cudaStreamCaptureModeThreadLocal));
       int rc = tc_generate(m, n, io, m->cap_stream, split ? half + 1 : 0);
       cudaError_t ce = cudaStreamEndCapture(m->cap_stream, &graph);
+      if (!rc && ce == cudaSuccess && graph && (io->done_flag || io->ready_flag)) {
+        // find the two nodes whose arguments carry the per-call epoch
+        size_t nn = 0;
+        cudaGraphGetNodes(graph, nullptr, &nn);
+        std::vector<cudaGraphNode_t> nodes(nn);
+        cudaGraphGetNodes(graph, nodes.data(), &nn);
+        for (cudaGraphNode_t nd : nodes) {
+          cudaGraphNodeType ty;
+          if (cudaGraphNodeGetType(nd, &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+          cudaKernelNodeParams kp{};
+          if (cudaGraphKernelNodeGetParams(nd, &kp) != cudaSuccess) continue;
+          if (kp.func == reinterpret_cast<void *>(wait_flags_kernel)) e.ready_node = nd;
+          if (kp.func == reinterpret_cast<void *>(tc_signal_done_kernel)) e.done_node = nd;
+        }
+        if ((io->done_flag && !e.done_node) || (io->ready_flag && !e.ready_node)) ce = cudaErrorUnknown;
+      }
       cudaGraphExec_t exec = nullptr;
       if (!rc && ce == cudaSuccess && graph) ce = cudaGraphInstantiate(&exec, graph, 0);
+      if (graph && exec && (e.done_node || e.ready_node)) {
+        e.graph = graph;  // node handles stay valid only as long as their graph does
+        graph = nullptr;
+      }
       if (graph) cudaGraphDestroy(graph);
       if (rc || ce != cudaSuccess || !exec) {
         if (e.exec) cudaGraphExecDestroy(e.exec);
+        if (e.graph) cudaGraphDestroy(e.graph);
         if (rc) return rc;
         cudaGetLastError();  // capture not possible here: run eagerly from now on
         m->use_graph = false;
@@ -285,12 +330,14 @@ int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
       e.launches += m->last_launches;
     }
     e.n = n; e.rfloats = io->rfloats; e.output = io->output; e.logits = m->debug_logits;
+    e.done_flag = io->done_flag; e.ready_flag = io->ready_flag;
     if (m->graphs.size() >= 8) {  // evict the least recently used
       size_t victim = 0;
       for (size_t i = 1; i < m->graphs.size(); ++i)
         if (m->graphs[i].last_use < m->graphs[victim].last_use) victim = i;
       cudaGraphExecDestroy(m->graphs[victim].exec);
       if (m->graphs[victim].exec_tail) cudaGraphExecDestroy(m->graphs[victim].exec_tail);
+      if (m->graphs[victim].graph) cudaGraphDestroy(m->graphs[victim].graph);
       m->graphs[victim] = e;
       return launch(m->graphs[victim]);
     }

@@ -652,8 +652,8 @@ __device__ __forceinline__ void persist_fc(const PersistMaps &maps, const Persis
         st_shared_cluster_f32(seg_remote + (uint32_t)(((it & 1) * 4 + seg) * kTileM + rl) * 4u, my_sum);
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive_cluster(xbar_local);
-          mbar_arrive_cluster(xbar_remote);
+          mbar_arrive_release_cluster(xbar_local);
+          mbar_arrive_release_cluster(xbar_remote);
         }
         mbar_wait_cluster(xbar, (uint32_t)it & 1u);
         tl.stamp((step << 8) | 11);

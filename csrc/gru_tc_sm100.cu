@@ -18,11 +18,14 @@
 //   epilogue: r = s(acc_r + b_r), z = s(acc_z + b_z),
 //             n = tanh(acc_ni + b_in + r * (acc_nh + b_hn)), h' = n + z (h - n)
 //
-//   layer 0: x is the ONE-HOT row of the current character and Wx is the table
-//            T0[c] = W_i*0 . emb[c] + biases (computed once at init), so the
-//            embedding lookup and the three input matvecs (ref:669, :676,
-//            :702, :729) ride the tensor core as K = NUM_CHAR extra columns
-//            instead of being gathered per thread.
+//   layer 0: there is no x-part GEMM.  The embedding lookup and the three input
+//            matvecs (ref:669, :676, :702, :729) only depend on the character
+//            id, so they are the table T0[c] = W_i*0 . emb[c] + biases computed
+//            once at init; the epilogue thread of (name, 32 units) fetches its
+//            192 bytes of the name's row (bf16, six 32-byte loads) and adds them
+//            to the recurrent accumulators.  (An earlier version fed a one-hot
+//            row through the tensor core as K = NUM_CHAR extra columns: 20% of
+//            layer 0's MMA time spent multiplying by zeros.)
 //   layer l: x is the layer below's fresh hidden state (ref:773, :797, :821).
 //
 // FC (fc_sample_kernel): acc[128 names, C] = h_top . W_fc^T, then per name
@@ -77,6 +80,11 @@ struct LayerArgs {
   // 450-600 GB/s); wide panels spread a TMA box over more L2 slices.
   int pw_log2;      // log2(panel width in elements)
   int bpad;         // rows per panel
+  // layer 0 only: the folded input table, [H/64][C][2 halves][2 chunks][n|r|z][16] bf16,
+  // and the current character of every name
+  const __nv_bfloat16 *t0q;
+  const int32_t *chars;
+  int num_char;
   const float *bias;            // [H/64, 4, 64]: b_in, b_r, b_z, b_hn
   const __nv_bfloat16 *h_prev;  // [bpad, H]
   __nv_bfloat16 *h_out;         // [bpad, H]
@@ -114,34 +122,66 @@ __device__ __forceinline__ void tp_wait_counter(const uint32_t *p, uint32_t expe
   while ((int32_t)(ld_acquire_sys(p) - expect) < 0) __nanosleep(64);
 }
 
+// 32-byte read-only global load (one request instead of two 16-byte ones: the
+// table rows below are scattered per lane, so L1TEX wavefronts are what they cost)
+__device__ __forceinline__ void ldg256(const void *p, uint32_t (&v)[8]) {
+  asm volatile("ld.global.nc.L2::128B.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "l"(p));
+}
+
 // Gate math for one thread's (name, 32 units) slice of a finished tile:
 // t addresses this warp's TMEM lanes at the slice's first n_i column.  The bf16
 // result goes to the 128B-swizzled staging tile (row `r`, 16-byte chunks
 // half*4 .. half*4+3), from where one thread TMA-stores the whole tile.
+//   LAYER0: the x-part is not in TMEM; it is this name's row of the folded input
+//           table (t0 -> [2 chunks][n|r|z][16] bf16, biases included), and the
+//           accumulator only exists if the step has a recurrent half (has_acc).
+//           Nothing needs re-zeroing: the tile's first MMA overwrites.
+struct T0Rows { uint32_t v[2][3][8]; };  // [chunk][n|r|z][8 bf16 pairs] of one (name, 32 units)
+__device__ __forceinline__ void load_t0_rows(const __nv_bfloat16 *t0, T0Rows &q) {
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch)
+#pragma unroll
+    for (int g = 0; g < 3; ++g) ldg256(t0 + ch * 48 + g * 16, q.v[ch][g]);
+}
+
+template <bool LAYER0>
 __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
                                               const float4 *bias4, uint8_t *stage_tile,
-                                              int r, int half) {
+                                              int r, int half, const T0Rows &tq, bool has_acc) {
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     uint32_t vn[16], vr[16], vz[16], vh[16];
-    tmem_ld16(t + ch * 16, vn);
-    tmem_ld16(t + 64 + ch * 16, vr);
-    tmem_ld16(t + 128 + ch * 16, vz);
-    tmem_ld16(t + 192 + ch * 16, vh);
-    tmem_ld_wait();
+    const uint32_t (&tn)[8] = tq.v[ch][0];
+    const uint32_t (&tr)[8] = tq.v[ch][1];
+    const uint32_t (&tz)[8] = tq.v[ch][2];
+    if (!LAYER0 || has_acc) {
+      if (!LAYER0) tmem_ld16(t + ch * 16, vn);
+      tmem_ld16(t + 64 + ch * 16, vr);
+      tmem_ld16(t + 128 + ch * 16, vz);
+      tmem_ld16(t + 192 + ch * 16, vh);
+      tmem_ld_wait();
+    } else {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) vr[i] = vz[i] = vh[i] = 0u;
+    }
     const uint32_t hw[8] = {hq[2 * ch].x,     hq[2 * ch].y,     hq[2 * ch].z,
                             hq[2 * ch].w,     hq[2 * ch + 1].x, hq[2 * ch + 1].y,
                             hq[2 * ch + 1].z, hq[2 * ch + 1].w};
     uint32_t packed[8];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {  // 4 units per float4 of bias
-      const float4 b_in = __ldg(bias4 + ch * 4 + q);
-      const float4 b_r = __ldg(bias4 + 16 + ch * 4 + q);
-      const float4 b_z = __ldg(bias4 + 32 + ch * 4 + q);
+      float bi[4] = {0.f, 0.f, 0.f, 0.f}, br[4] = {0.f, 0.f, 0.f, 0.f}, bz[4] = {0.f, 0.f, 0.f, 0.f};
+      if (!LAYER0) {
+        const float4 b_in = __ldg(bias4 + ch * 4 + q);
+        const float4 b_r = __ldg(bias4 + 16 + ch * 4 + q);
+        const float4 b_z = __ldg(bias4 + 32 + ch * 4 + q);
+        bi[0] = b_in.x; bi[1] = b_in.y; bi[2] = b_in.z; bi[3] = b_in.w;
+        br[0] = b_r.x; br[1] = b_r.y; br[2] = b_r.z; br[3] = b_r.w;
+        bz[0] = b_z.x; bz[1] = b_z.y; bz[2] = b_z.z; bz[3] = b_z.w;
+      }
       const float4 b_hn = __ldg(bias4 + 48 + ch * 4 + q);
-      const float bi[4] = {b_in.x, b_in.y, b_in.z, b_in.w};
-      const float br[4] = {b_r.x, b_r.y, b_r.z, b_r.w};
-      const float bz[4] = {b_z.x, b_z.y, b_z.z, b_z.w};
       const float bh[4] = {b_hn.x, b_hn.y, b_hn.z, b_hn.w};
       float hn[4];
 #pragma unroll
@@ -149,10 +189,20 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
         const int i = q * 4 + e;
         const uint32_t w = hw[i >> 1];
         const float hp = __uint_as_float((i & 1) ? (w & 0xFFFF0000u) : (w << 16));
-        const float rr = sigmoid_approx(__uint_as_float(vr[i]) + br[e]);
-        const float z = sigmoid_approx(__uint_as_float(vz[i]) + bz[e]);
-        const float nn = tanh_approx(fmaf(rr, __uint_as_float(vh[i]) + bh[e],
-                                          __uint_as_float(vn[i]) + bi[e]));
+        float xn, xr, xz;
+        if (LAYER0) {   // table row: bf16 pairs, biases already folded in
+          const uint32_t wn = tn[i >> 1], wr = tr[i >> 1], wz = tz[i >> 1];
+          xn = __uint_as_float((i & 1) ? (wn & 0xFFFF0000u) : (wn << 16));
+          xr = __uint_as_float((i & 1) ? (wr & 0xFFFF0000u) : (wr << 16));
+          xz = __uint_as_float((i & 1) ? (wz & 0xFFFF0000u) : (wz << 16));
+        } else {        // x-part sits in the same accumulator columns as the h-part (r, z) / next to it (n)
+          xn = __uint_as_float(vn[i]) + bi[e];
+          xr = br[e];
+          xz = bz[e];
+        }
+        const float rr = sigmoid_approx(__uint_as_float(vr[i]) + xr);
+        const float z = sigmoid_approx(__uint_as_float(vz[i]) + xz);
+        const float nn = tanh_approx(fmaf(rr, __uint_as_float(vh[i]) + bh[e], xn));
         // h' = (1-z)*n + z*h  ==  n + z*(h - n)     (ref:752-763)
         hn[e] = fmaf(z, hp - nn, nn);
       }
@@ -169,13 +219,15 @@ __device__ __forceinline__ void gate_epilogue(uint32_t t, const uint4 (&hq)[4],
     *reinterpret_cast<uint4 *>(rowp + (((c0 + 1) ^ (r & 7)) << 4)) =
         make_uint4(packed[4], packed[5], packed[6], packed[7]);
   }
-  // re-zero this warp's n_h columns before the stage goes back to the MMAs
-  uint32_t zero[16];
+  if (!LAYER0) {
+    // re-zero this warp's n_h columns before the stage goes back to the MMAs
+    uint32_t zero[16];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) zero[i] = 0u;
-  tmem_st16(t + 192, zero);
-  tmem_st16(t + 192 + 16, zero);
-  tmem_st_wait();
+    for (int i = 0; i < 16; ++i) zero[i] = 0u;
+    tmem_st16(t + 192, zero);
+    tmem_st16(t + 192 + 16, zero);
+    tmem_st_wait();
+  }
 }
 
 // Tail of a tile's epilogue, run by every epilogue thread (tid = 0..255).
@@ -301,6 +353,7 @@ __device__ __forceinline__ void produce_part(const CUtensorMap *map_a, const CUt
   }
 }
 
+template <bool LAYER0>
 __global__ void __launch_bounds__(L_THREADS, 1)
 gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
                  const __grid_constant__ CUtensorMap map_h,
@@ -325,8 +378,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
   const int kb_total = args.kb_x + args.kb_h;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&map_x);
-    tma_prefetch_desc(&map_wx);
+    if (args.kb_x) { tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_wx); }
     if (args.kb_h) { tma_prefetch_desc(&map_h); tma_prefetch_desc(&map_wh); }
   }
   if (warp == 1 && lane == 0) {
@@ -394,7 +446,8 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
     uint32_t acc_phase = 0;
     const uint32_t idesc = umma_idesc_bf16(kTileM, 192);
     const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    // layer 0, step 0 has no GEMM at all (no x-part, h == 0): nothing to issue
+    for (int tile = blockIdx.x; tile < total_tiles && kb_total > 0; tile += gridDim.x) {
       mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
@@ -409,8 +462,9 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
             umma_bf16(d, da + 2, db + 2, idesc, 1u);
             umma_bf16(d, da + 4, db + 4, idesc, 1u);
             umma_bf16(d, da + 6, db + 6, idesc, 1u);
-          } else {               // [r | z | n_h]: accumulates (n_h pre-zeroed)
-            umma_bf16(d + 64, da, db, idesc, 1u);
+          } else {               // [r | z | n_h]: accumulates (n_h pre-zeroed); layer 0 has no
+                                 // x-part, there the first MMA overwrites all three
+            umma_bf16(d + 64, da, db, idesc, (args.kb_x == 0 && kb == 0) ? 0u : 1u);
             umma_bf16(d + 64, da + 2, db + 2, idesc, 1u);
             umma_bf16(d + 64, da + 4, db + 4, idesc, 1u);
             umma_bf16(d + 64, da + 6, db + 6, idesc, 1u);
@@ -441,6 +495,11 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
     uint32_t acc_phase = 0;
     uint8_t *stage_out = smem + L_STAGES * L_STAGE_BYTES + 1024;  // after the barrier block
     const bool issuer = (warp == 4 && lane == 0);
+    int c_next = 0;  // layer 0: character of this thread's name in the upcoming tile
+    if (LAYER0 && (int)blockIdx.x < total_tiles) {
+      const int row0 = ((int)blockIdx.x / args.n_blocks) * kTileM + (warp & 3) * 32 + lane;
+      c_next = row0 < args.n ? args.chars[row0] : 0;
+    }
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int m_tile = tile / args.n_blocks;
@@ -463,20 +522,38 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       }
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
+      // layer 0: this thread's 192 bytes of the name's row of the folded input
+      // table, requested before the accumulator wait like h_prev above; the
+      // character of the NEXT tile's name is requested one tile ahead
+      T0Rows tq;
+      if (LAYER0) {
+        const int c = c_next;
+        const int tile2 = tile + (int)gridDim.x;
+        if (tile2 < total_tiles) {
+          const int row2 = (tile2 / args.n_blocks) * kTileM + r;
+          c_next = row2 < args.n ? args.chars[row2] : 0;
+        }
+        load_t0_rows(args.t0q + (((size_t)n_blk * args.num_char + c) * 2 + half) * 96, tq);
+      }
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
       // the TMA store that read this staging buffer two tiles ago is done
       if (issuer) tma_store_wait_read<1>();
       named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
 
-      mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
-      tc_fence_after();
+      const bool has_acc = kb_total > 0;
+      if (has_acc) {
+        mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
+        tc_fence_after();
+      }
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
-      gate_epilogue(t, hq, bias4, stage_tile, r, half);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);  // TMEM stage back to the MMAs
+      gate_epilogue<LAYER0>(t, hq, bias4, stage_tile, r, half, tq, has_acc);
+      if (has_acc) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);  // TMEM stage back to the MMAs
+      }
       epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, pub, it);
-      if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+      if (has_acc && ++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
     if (issuer) tma_store_wait<0>();  // smem must outlive the store's reads
   }
@@ -504,6 +581,7 @@ constexpr int P_STAGE_BYTES = TC_A_BYTES + P_B_BYTES;
 constexpr int P_STAGES = 6;
 constexpr int P_SMEM_BYTES = 1024 + P_STAGES * P_STAGE_BYTES + 1024 + 2 * OUT_TILE_BYTES;
 
+template <bool LAYER0>
 __global__ void __launch_bounds__(L_THREADS, 1)
 gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
                       const __grid_constant__ CUtensorMap map_h,
@@ -533,8 +611,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
   const int kb_total = args.kb_x + args.kb_h;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&map_x);
-    tma_prefetch_desc(&map_wx);
+    if (args.kb_x) { tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_wx); }
     if (args.kb_h) { tma_prefetch_desc(&map_h); tma_prefetch_desc(&map_wh); }
   }
   if (warp == 1 && lane == 0) {
@@ -600,7 +677,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       uint32_t acc_phase = 0;
       const uint32_t idesc = umma_idesc_bf16(2 * kTileM, 192);
       const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
-      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+      for (int tile = pair; tile < total_tiles && kb_total > 0; tile += num_pairs) {
         mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
@@ -615,8 +692,8 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
               umma_bf16_2sm(d, da + 2, db + 2, idesc, 1u);
               umma_bf16_2sm(d, da + 4, db + 4, idesc, 1u);
               umma_bf16_2sm(d, da + 6, db + 6, idesc, 1u);
-            } else {
-              umma_bf16_2sm(d + 64, da, db, idesc, 1u);
+            } else {   // layer 0 (no x-part): the first MMA overwrites
+              umma_bf16_2sm(d + 64, da, db, idesc, (args.kb_x == 0 && kb == 0) ? 0u : 1u);
               umma_bf16_2sm(d + 64, da + 2, db + 2, idesc, 1u);
               umma_bf16_2sm(d + 64, da + 4, db + 4, idesc, 1u);
               umma_bf16_2sm(d + 64, da + 6, db + 6, idesc, 1u);
@@ -646,6 +723,11 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     uint32_t acc_phase = 0;
     uint8_t *stage_out = smem + P_STAGES * P_STAGE_BYTES + 1024;  // after the barrier block
     const bool issuer = (warp == 4 && lane == 0);
+    int c_next = 0;  // layer 0: character of this thread's name in the upcoming tile
+    if (LAYER0 && pair < total_tiles) {
+      const int row0 = ((pair / args.n_blocks) * 2 + (int)rank) * kTileM + (warp & 3) * 32 + lane;
+      c_next = row0 < args.n ? args.chars[row0] : 0;
+    }
     int it = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
       const int m2 = tile / args.n_blocks;
@@ -667,19 +749,34 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       }
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
+      T0Rows tq;  // layer 0: see gru_layer_kernel
+      if (LAYER0) {
+        const int c = c_next;
+        const int tile2 = tile + num_pairs;
+        if (tile2 < total_tiles) {
+          const int row2 = ((tile2 / args.n_blocks) * 2 + (int)rank) * kTileM + r;
+          c_next = row2 < args.n ? args.chars[row2] : 0;
+        }
+        load_t0_rows(args.t0q + (((size_t)n_blk * args.num_char + c) * 2 + half) * 96, tq);
+      }
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
       if (issuer) tma_store_wait_read<1>();
       named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
 
-      mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
-      tc_fence_after();
+      const bool has_acc = kb_total > 0;
+      if (has_acc) {
+        mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
+        tc_fence_after();
+      }
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
-      gate_epilogue(t, hq, bias4, stage_tile, r, half);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
+      gate_epilogue<LAYER0>(t, hq, bias4, stage_tile, r, half, tq, has_acc);
+      if (has_acc) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
+      }
       epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, pub, it);
-      if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+      if (has_acc && ++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
     if (issuer) tma_store_wait<0>();  // smem must outlive the store's reads
   }
@@ -702,14 +799,13 @@ constexpr int F_STAGES = 4;
 constexpr int F_SMEM_BYTES = 1024 + F_STAGES * F_STAGE_BYTES + 4096;
 
 struct FcArgs {
-  int n, m_tiles, kb, H, C, T, step, eos, kx;  // kx = one-hot row length
+  int n, m_tiles, kb, H, C, T, step, eos;
   const float *b_fc;
   float *logits;            // optional [bpad, C] tap (tests / debugging)
   const float *rfloats;     // [n, T]   (may be a peer address)
   char *output;             // [n, T+1] (may be a peer address)
   int32_t *chars;
   uint8_t *alive;
-  __nv_bfloat16 *onehot;    // [bpad, kx]
   // tensor parallel: the top layer's hidden buffer arrives in per-rank chunks
   int tp_world, tp_rank, kb_rank, flag_stride;
   uint32_t expect_h;
@@ -831,7 +927,6 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
       // this step's random float: fetched (possibly over NVLink from the root
       // rank's buffer — the MPI_Scatter of ref:636) before the accumulator wait
       const float r = live ? args.rfloats[(size_t)row * args.T + args.step] : 2.0f;
-      const int old_char = (valid && half == 0) ? args.chars[row] : 0;
       mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
       tc_fence_after();
       const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * TC_ACC_STRIDE;
@@ -893,11 +988,7 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
           for (int l = 1; l <= args.T; ++l) orow[l] = 0;  // NUL pad, ref:643
         if (live) {
           orow[args.step] = (char)sel;  // EOS id is written too, ref:877
-          args.chars[row] = sel;
-          // next step's layer-0 input: move the 1 in this name's one-hot row
-          __nv_bfloat16 *oh = args.onehot + (size_t)row * args.kx;
-          oh[old_char] = __float2bfloat16_rn(0.0f);
-          oh[sel] = __float2bfloat16_rn(1.0f);
+          args.chars[row] = sel;  // next step's layer-0 input: the row of the folded table it picks
           if (sel == args.eos) args.alive[row] = 0;  // ref:881
         }
       }
@@ -941,27 +1032,28 @@ __global__ void to_bf16_kernel(const float *__restrict__ src,
   if (idx < n) dst[(idx / cols) * ld + idx % cols] = __float2bfloat16_rn(src[idx]);
 }
 
-// Layer-0 "x weights": t0w[jb][slot][u][c], slots (n, r, z), K = kx >= C:
-//   W_i{g}0 . emb[c] + b_i{g}0 (+ b_h{g}0 for r, z); zero for c >= C.
+// Layer-0 input table for the epilogue gather:
+//   t0q[jb][c][half][chunk][slot: n,r,z][16] = W_i{g}0 . emb[c] + b_i{g}0 (+ b_h{g}0 for r, z)
+// for hidden unit unit0 + jb*64 + half*32 + chunk*16 + u, so that the 192 bytes one
+// epilogue thread (name, 32 units) needs are contiguous.
 __global__ void pack_t0_kernel(const float *__restrict__ t0_raw,
                                const float *__restrict__ b_ih,
                                const float *__restrict__ b_hh,
-                               __nv_bfloat16 *__restrict__ t0w, int C, int H,
-                               int Hs, int unit0, int kx) {
+                               __nv_bfloat16 *__restrict__ t0q, int C, int H,
+                               int Hs, int unit0) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (size_t)3 * Hs * kx) return;
-  int c = (int)(idx % kx);
-  size_t prow = idx / kx;
-  int jb = (int)(prow / 192), rem = (int)(prow % 192);
-  int slot = rem / 64, u = rem % 64;
-  int g = slot == 0 ? 2 : slot - 1;  // slots (n, r, z) <- gates (2, 0, 1)
-  int i = unit0 + jb * 64 + u;
-  float v = 0.0f;
-  if (c < C) {
-    v = t0_raw[(size_t)c * 3 * H + g * H + i] + b_ih[g * H + i];
-    if (g < 2) v += b_hh[g * H + i];
-  }
-  t0w[idx] = __float2bfloat16_rn(v);
+  if (idx >= (size_t)3 * Hs * C) return;
+  const int u = (int)(idx % 16);
+  const int slot = (int)((idx / 16) % 3);
+  const int chunk = (int)((idx / 48) % 2);
+  const int half = (int)((idx / 96) % 2);
+  const int c = (int)((idx / 192) % C);
+  const int jb = (int)(idx / ((size_t)192 * C));
+  const int g = slot == 0 ? 2 : slot - 1;  // slots (n, r, z) <- gates (2, 0, 1)
+  const int i = unit0 + jb * 64 + half * 32 + chunk * 16 + u;
+  float v = t0_raw[(size_t)c * 3 * H + g * H + i] + b_ih[g * H + i];
+  if (g < 2) v += b_hh[g * H + i];
+  t0q[idx] = __float2bfloat16_rn(v);
 }
 
 // bias[jb][q][u]: q=0 b_in, q=1 b_ir+b_hr, q=2 b_iz+b_hz, q=3 b_hn.
@@ -982,19 +1074,12 @@ __global__ void pack_bias_kernel(const float *__restrict__ b_ih,
   out[idx] = v;
 }
 
-// Per-call reset: chars = SOS (ref:652), alive flags, one-hot rows = e_SOS.
-__global__ void tc_init_kernel(int32_t *chars, uint8_t *alive,
-                               __nv_bfloat16 *onehot, int n, int rows, int kx,
-                               int sos) {
-  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  size_t total = (size_t)rows * kx;
-  if (idx < total) {
-    int c = (int)(idx % kx);
-    onehot[idx] = __float2bfloat16_rn(c == sos ? 1.0f : 0.0f);
-  }
-  if (idx < (size_t)rows) {
+// Per-call reset: chars = SOS (ref:652), alive flags.
+__global__ void tc_init_kernel(int32_t *chars, uint8_t *alive, int n, int rows, int sos) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < rows) {
     chars[idx] = sos;
-    alive[idx] = idx < (size_t)n;
+    alive[idx] = idx < n;
   }
 }
 
@@ -1094,8 +1179,6 @@ int tc_prepare(b200gru_model *m) {
   LayoutIndex ix(L);
   const unsigned TPB = 256;
   auto blocks = [&](size_t n) { return (unsigned)((n + TPB - 1) / TPB); };
-  const int kx = (C + 63) / 64 * 64;
-  m->kx = kx;
   const int ld = m->ldh;
   {
     // panel width of the hidden buffers: row-major unless tensor parallel, where
@@ -1107,16 +1190,10 @@ int tc_prepare(b200gru_model *m) {
     while ((1 << m->pw_log2) < pw) ++m->pw_log2;
   }
 
-  // layer-0 input: one-hot rows and the T0 table as a K-major weight
-  if (int rc = tc_alloc(m, &m->onehot, (size_t)m->bpad * kx)) return rc;
-  B200_CUDA(cudaMemset(m->onehot, 0, sizeof(__nv_bfloat16) * (size_t)m->bpad * kx));
-  if (int rc = make_tmap_bf16_2d(&m->map_onehot, m->onehot, (uint64_t)m->bpad, kx, kTileM, 64))
-    return rc;
-  if (int rc = tc_alloc(m, &m->t0w, (size_t)3 * Hs * kx)) return rc;
-  pack_t0_kernel<<<blocks((size_t)3 * Hs * kx), TPB>>>(
-      m->t0_raw, m->P(ix.b_i(0, 0)), m->P(ix.b_h(0, 0)), m->t0w, C, H, Hs, unit0, kx);
-  if (int rc = make_tmap_bf16_2d(&m->map_t0w, m->t0w, 3 * (uint64_t)Hs, kx, 192, 64)) return rc;
-  if (int rc = make_tmap_bf16_2d(&m->map_t0w_p, m->t0w, 3 * (uint64_t)Hs, kx, 96, 64)) return rc;
+  // layer-0 input: the folded table, gathered by the epilogue
+  if (int rc = tc_alloc(m, &m->t0q, (size_t)3 * Hs * C)) return rc;
+  pack_t0_kernel<<<blocks((size_t)3 * Hs * C), TPB>>>(
+      m->t0_raw, m->P(ix.b_i(0, 0)), m->P(ix.b_h(0, 0)), m->t0q, C, H, Hs, unit0);
 
   for (int l = 0; l < L; ++l) {
     TcLayer &t = m->tc[l];
@@ -1155,9 +1232,13 @@ int tc_prepare(b200gru_model *m) {
   if (int rc = make_tmap_bf16_2d(&m->map_w_fc, m->w_fc, (uint64_t)C, H, C, 64, ld)) return rc;
   B200_CUDA(cudaGetLastError());
 
-  B200_CUDA(cudaFuncSetAttribute(gru_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  B200_CUDA(cudaFuncSetAttribute(gru_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  L_SMEM_BYTES));
-  B200_CUDA(cudaFuncSetAttribute(gru_layer_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  B200_CUDA(cudaFuncSetAttribute(gru_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 L_SMEM_BYTES));
+  B200_CUDA(cudaFuncSetAttribute(gru_layer_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 P_SMEM_BYTES));
+  B200_CUDA(cudaFuncSetAttribute(gru_layer_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  P_SMEM_BYTES));
   {
     const char *e = getenv("B200GRU_CTA_PAIRS");
@@ -1210,9 +1291,7 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
     for (int l = 0; l < L; ++l) m->tp_rounds[l][0] = m->tp_rounds[l][1] = 0;
   }
   if (head) {
-    size_t total = (size_t)rows * m->kx;
-    tc_init_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(
-        m->chars, m->alive, m->onehot, n, rows, m->kx, c.sos);
+    tc_init_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(m->chars, m->alive, n, rows, c.sos);
     ++launches;
     m->trace_mark("init", s);
   }
@@ -1223,7 +1302,8 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
       TcLayer &t = m->tc[l];
       LayerArgs a{};
       a.n = n; a.m_tiles = m_tiles; a.n_blocks = Hs / kUnitBlock;
-      a.kb_x = (l == 0 ? m->kx : H) / TC_BLOCK_K;
+      a.kb_x = l == 0 ? 0 : H / TC_BLOCK_K;  // layer 0: table gather in the epilogue, no x-part GEMM
+      if (l == 0) { a.t0q = m->t0q; a.chars = m->chars; a.num_char = C; }
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
       a.pw_log2 = m->pw_log2; a.bpad = m->bpad; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
       a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.x_full = l > 0;
@@ -1268,18 +1348,18 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
           ++na;
           cfg.attrs = attr;
           cfg.numAttrs = na;
-          B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_pair_kernel,
-                                       l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-                                       l == 0 ? m->map_t0w_p : t.map_w_ih_p, t.map_w_hh_p,
+          B200_CUDA(cudaLaunchKernelEx(&cfg, l == 0 ? gru_layer_pair_kernel<true> : gru_layer_pair_kernel<false>,
+                                       l == 0 ? t.map_h[rd] : m->tc[l - 1].map_h[wr], t.map_h[rd],
+                                       l == 0 ? t.map_w_hh_p : t.map_w_ih_p, t.map_w_hh_p,
                                        t.map_h[wr], a));
         } else {
           cfg.gridDim = dim3(tiles < sms ? tiles : sms);
           cfg.dynamicSmemBytes = L_SMEM_BYTES;
           cfg.attrs = attr;
           cfg.numAttrs = na;
-          B200_CUDA(cudaLaunchKernelEx(&cfg, gru_layer_kernel,
-                                       l == 0 ? m->map_onehot : m->tc[l - 1].map_h[wr], t.map_h[rd],
-                                       l == 0 ? m->map_t0w : t.map_w_ih, t.map_w_hh, t.map_h[wr], a));
+          B200_CUDA(cudaLaunchKernelEx(&cfg, l == 0 ? gru_layer_kernel<true> : gru_layer_kernel<false>,
+                                       l == 0 ? t.map_h[rd] : m->tc[l - 1].map_h[wr], t.map_h[rd],
+                                       l == 0 ? t.map_w_hh : t.map_w_ih, t.map_w_hh, t.map_h[wr], a));
         }
       }
       ++launches;
@@ -1295,10 +1375,10 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
     }
     FcArgs a{};
     a.n = n; a.m_tiles = m_tiles; a.kb = H / TC_BLOCK_K; a.H = H; a.C = C; a.T = T;
-    a.step = step; a.eos = c.eos; a.kx = m->kx;
+    a.step = step; a.eos = c.eos;
     a.b_fc = m->b_fc; a.logits = m->debug_logits ? m->logits : nullptr;
     a.rfloats = io->rfloats; a.output = io->output;
-    a.chars = m->chars; a.alive = m->alive; a.onehot = m->onehot;
+    a.chars = m->chars; a.alive = m->alive;
     a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.flag_stride = mt_max;
     a.pw_log2 = m->pw_log2; a.bpad = m->bpad;
     if (W > 1) {

@@ -57,10 +57,7 @@ struct b200gru_model {
   int ldh = 0;                       // row stride (elements) of hidden buffers and K=H weights
                                      // (H + B200GRU_LD_PAD; padding measured: no effect, default 0)
   int pw_log2 = 0;                   // hidden buffers: [H/pw panels][bpad][pw], pw = 1 << pw_log2
-  int kx = 0;                        // one-hot row length: num_char rounded up to 64
-  __nv_bfloat16 *onehot = nullptr;   // [bpad, kx]  layer-0 x operand
-  __nv_bfloat16 *t0w = nullptr;      // [H/64][192][kx] layer-0 table as K-major weights
-  CUtensorMap map_onehot, map_t0w, map_t0w_p;
+  __nv_bfloat16 *t0q = nullptr;      // [H/64][C][2][2][n|r|z][16] folded layer-0 input table (epilogue gather)
   bool use_pdl = true;               // programmatic dependent launch between the step kernels
   bool use_pairs = true;             // cta_group::2 layer kernel (B200GRU_CTA_PAIRS=0 disables)
   bool debug_logits = false;         // FC kernel also stores pre-softmax logits
@@ -103,6 +100,12 @@ struct b200gru_model {
     bool logits = false;
     cudaGraphExec_t exec = nullptr;
     cudaGraphExec_t exec_tail = nullptr;  // second half when the call is split at `ready_event`
+    // data-parallel calls: the flag addresses are part of the key, the epoch
+    // VALUES change per call and are patched into these two kernel nodes
+    uint32_t *done_flag = nullptr;
+    const uint32_t *ready_flag = nullptr;
+    cudaGraphNode_t done_node = nullptr, ready_node = nullptr;
+    cudaGraph_t graph = nullptr;  // kept alive while the node handles above are in use
     int launches = 0;
     uint64_t last_use = 0;
   };
@@ -149,6 +152,7 @@ int gru_cell_fp32_run(const float *x, const float *h_in, const float *w_ih,
 // tensor-core path (gru_tc_sm100.cu)
 int tc_prepare(b200gru_model *m);
 int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, int part = 0);
+__global__ void tc_signal_done_kernel(uint32_t *flag, uint32_t value);
 // persistent path (gru_persist_sm100.cu)
 int persist_prepare(b200gru_model *m);
 int persist_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s);

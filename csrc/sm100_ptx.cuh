@@ -287,7 +287,16 @@ __device__ __forceinline__ uint32_t mapa_u32(const void *p, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(out) : "r"(smem_u32(p)), "r"(rank));
   return out;
 }
+// Arrive on an mbarrier of another CTA of the cluster.  Default semantics
+// (release at CTA scope): enough to hand a TMEM stage back — the tcgen05 fence
+// before it orders the TMEM reads — and free of the GPU-wide memory barrier the
+// cluster-scope release below costs.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// Same with a release at cluster scope: publishes this thread's prior
+// shared::cluster stores to the CTA that waits on the barrier.
+__device__ __forceinline__ void mbar_arrive_release_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr)
                : "memory");
 }

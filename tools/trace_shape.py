@@ -23,7 +23,7 @@ agg = {}
 for k, t in tr:
     agg.setdefault(k, []).append(t)
 H, B, C = cfg.hidden, a.names, cfg.num_char
-fl = {"layer0": 2.0 * B * 3 * H * (256 + H), "layerN": 2.0 * B * 3 * H * 2 * H, "fc_sample": 2.0 * B * C * H}
+fl = {"layer0": 2.0 * B * 3 * H * H, "layerN": 2.0 * B * 3 * H * 2 * H, "fc_sample": 2.0 * B * C * H}
 print(f"H={H} B={B}: " + "; ".join(
     f"{k}: steady {sorted(v)[len(v)//2]*1e3:.0f} us" + (f" = {fl[k]/(sorted(v)[len(v)//2]*1e-3)/1e12:.0f} TFLOP/s" if k in fl else "")
     for k, v in agg.items()))
