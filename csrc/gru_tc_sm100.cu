@@ -495,46 +495,44 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
     uint32_t acc_phase = 0;
     uint8_t *stage_out = smem + L_STAGES * L_STAGE_BYTES + 1024;  // after the barrier block
     const bool issuer = (warp == 4 && lane == 0);
-    int c_next = 0;  // layer 0: character of this thread's name in the upcoming tile
-    if (LAYER0 && (int)blockIdx.x < total_tiles) {
-      const int row0 = ((int)blockIdx.x / args.n_blocks) * kTileM + (warp & 3) * 32 + lane;
-      c_next = row0 < args.n ? args.chars[row0] : 0;
-    }
+    // Operands the gate math needs besides the accumulator — the previous state
+    // of this thread's 32 units and, for layer 0, its 192 bytes of the name's row
+    // of the folded input table — are requested ONE TILE AHEAD, right after the
+    // gate math of the tile before: when the epilogue is what paces the kernel
+    // the accumulator is always ready, so loads issued at the top of a tile would
+    // have nothing to hide behind.  The character itself is fetched two tiles ahead.
+    const int r = quarter * 32 + lane;
+    const bool has_h = args.kb_h > 0;
+    uint4 hq[4];
+    T0Rows tq;
+    int c_next = 0;
+    auto char_of = [&](int tile_q) -> int {
+      if (!LAYER0 || tile_q >= total_tiles) return 0;
+      const int row_q = (tile_q / args.n_blocks) * kTileM + r;
+      return row_q < args.n ? args.chars[row_q] : 0;
+    };
+    auto request = [&](int tile_q, int c) {
+      if (tile_q >= total_tiles) return;
+      const int mq = tile_q / args.n_blocks, nq = tile_q % args.n_blocks;
+      if (has_h) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(
+            args.h_prev + h_offset(mq * kTileM + r, args.col0 + nq * 64 + half * 32, args.pw_log2, args.bpad));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hq[i] = src[i];
+      }
+      if (LAYER0) load_t0_rows(args.t0q + (((size_t)nq * args.num_char + c) * 2 + half) * 96, tq);
+    };
+#pragma unroll
+    for (int i = 0; i < 4; ++i) hq[i] = make_uint4(0, 0, 0, 0);
+    request((int)blockIdx.x, char_of((int)blockIdx.x));
+    c_next = char_of((int)blockIdx.x + (int)gridDim.x);
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int m_tile = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
-      const int r = quarter * 32 + lane;
-      const int row = m_tile * kTileM + r;
-      const bool has_h = args.kb_h > 0;
       const int col = args.col0 + n_blk * 64;
-      const size_t hoff = h_offset(row, col + half * 32, args.pw_log2, args.bpad);
-      // previous hidden for this thread's 32 units: issue the loads before
-      // waiting on the accumulator so their latency hides behind the MMAs
-      uint4 hq[4];
-      if (has_h) {
-        const uint4 *src = reinterpret_cast<const uint4 *>(args.h_prev + hoff);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hq[i] = src[i];
-      } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hq[i] = make_uint4(0, 0, 0, 0);
-      }
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
-      // layer 0: this thread's 192 bytes of the name's row of the folded input
-      // table, requested before the accumulator wait like h_prev above; the
-      // character of the NEXT tile's name is requested one tile ahead
-      T0Rows tq;
-      if (LAYER0) {
-        const int c = c_next;
-        const int tile2 = tile + (int)gridDim.x;
-        if (tile2 < total_tiles) {
-          const int row2 = (tile2 / args.n_blocks) * kTileM + r;
-          c_next = row2 < args.n ? args.chars[row2] : 0;
-        }
-        load_t0_rows(args.t0q + (((size_t)n_blk * args.num_char + c) * 2 + half) * 96, tq);
-      }
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
       // the TMA store that read this staging buffer two tiles ago is done
       if (issuer) tma_store_wait_read<1>();
@@ -551,6 +549,11 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);  // TMEM stage back to the MMAs
+      }
+      {  // next tile's operands, and the character of the tile after it
+        const int c = c_next;
+        c_next = char_of(tile + 2 * (int)gridDim.x);
+        request(tile + (int)gridDim.x, c);
       }
       epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, pub, it);
       if (has_acc && ++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
@@ -723,42 +726,41 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     uint32_t acc_phase = 0;
     uint8_t *stage_out = smem + P_STAGES * P_STAGE_BYTES + 1024;  // after the barrier block
     const bool issuer = (warp == 4 && lane == 0);
-    int c_next = 0;  // layer 0: character of this thread's name in the upcoming tile
-    if (LAYER0 && pair < total_tiles) {
-      const int row0 = ((pair / args.n_blocks) * 2 + (int)rank) * kTileM + (warp & 3) * 32 + lane;
-      c_next = row0 < args.n ? args.chars[row0] : 0;
-    }
+    // next tile's h_prev / table rows are requested one tile ahead, its character
+    // two tiles ahead (see gru_layer_kernel)
+    const int r = quarter * 32 + lane;
+    const bool has_h = args.kb_h > 0;
+    uint4 hq[4];
+    T0Rows tq;
+    int c_next = 0;
+    auto char_of = [&](int tile_q) -> int {
+      if (!LAYER0 || tile_q >= total_tiles) return 0;
+      const int row_q = ((tile_q / args.n_blocks) * 2 + (int)rank) * kTileM + r;
+      return row_q < args.n ? args.chars[row_q] : 0;
+    };
+    auto request = [&](int tile_q, int c) {
+      if (tile_q >= total_tiles) return;
+      const int mq = (tile_q / args.n_blocks) * 2 + (int)rank, nq = tile_q % args.n_blocks;
+      if (has_h) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(
+            args.h_prev + h_offset(mq * kTileM + r, args.col0 + nq * 64 + half * 32, args.pw_log2, args.bpad));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hq[i] = src[i];
+      }
+      if (LAYER0) load_t0_rows(args.t0q + (((size_t)nq * args.num_char + c) * 2 + half) * 96, tq);
+    };
+#pragma unroll
+    for (int i = 0; i < 4; ++i) hq[i] = make_uint4(0, 0, 0, 0);
+    request(pair, char_of(pair));
+    c_next = char_of(pair + num_pairs);
     int it = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
       const int m2 = tile / args.n_blocks;
       const int n_blk = tile % args.n_blocks;
       const int m_tile = m2 * 2 + (int)rank;
-      const int r = quarter * 32 + lane;
-      const int row = m_tile * kTileM + r;
-      const bool has_h = args.kb_h > 0;
       const int col = args.col0 + n_blk * 64;
-      const size_t hoff = h_offset(row, col + half * 32, args.pw_log2, args.bpad);
-      uint4 hq[4];
-      if (has_h) {
-        const uint4 *src = reinterpret_cast<const uint4 *>(args.h_prev + hoff);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hq[i] = src[i];
-      } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hq[i] = make_uint4(0, 0, 0, 0);
-      }
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
-      T0Rows tq;  // layer 0: see gru_layer_kernel
-      if (LAYER0) {
-        const int c = c_next;
-        const int tile2 = tile + num_pairs;
-        if (tile2 < total_tiles) {
-          const int row2 = ((tile2 / args.n_blocks) * 2 + (int)rank) * kTileM + r;
-          c_next = row2 < args.n ? args.chars[row2] : 0;
-        }
-        load_t0_rows(args.t0q + (((size_t)n_blk * args.num_char + c) * 2 + half) * 96, tq);
-      }
       uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
       if (issuer) tma_store_wait_read<1>();
       named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
@@ -774,6 +776,11 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc_stage], 0));
+      }
+      {  // next tile's operands, and the character of the tile after it
+        const int c = c_next;
+        c_next = char_of(tile + 2 * num_pairs);
+        request(tile + num_pairs, c);
       }
       epilogue_store_tile(&map_out, args, stage_tile, col, m_tile, issuer, threadIdx.x - 128, pub, it);
       if (has_acc && ++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
