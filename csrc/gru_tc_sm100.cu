@@ -915,19 +915,24 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
     }
   } else if (warp >= 4) {
     // Two threads per name (same TMEM lane): half 0 (warps 4-7) owns columns
-    // [0, split), half 1 (warps 8-11) owns [split, C).  Partial sums and the
-    // second half's result cross over through a few words of shared memory.
+    // [0, split), half 1 (warps 8-11) owns [split, C).  Pass 1 turns the logits
+    // into exponentials (kept in TMEM in place) and keeps one sum per 16 columns
+    // in registers; the two halves swap their totals through shared memory.
+    // With both totals every thread knows where its half starts in the CDF and
+    // therefore which half — and which 16-column block of it — contains the
+    // sampled point; only that thread walks, 16 columns at most, and does the
+    // name's bookkeeping.
     const int quarter = warp & 3;
     const int half = (warp - 4) >> 2;
     const int rl = quarter * 32 + lane;           // row within the tile
     const int split = ((C / 16 + 1) / 2) * 16;
     const int cbeg = half == 0 ? 0 : split, cend = half == 0 ? split : C;
-    float *part_sum = reinterpret_cast<float *>(smem + F_STAGES * F_STAGE_BYTES + 512);  // [2][128]
-    int *part_sel = reinterpret_cast<int *>(part_sum + 2 * kTileM);                      // [128]
+    float *part_sum = reinterpret_cast<float *>(smem + F_STAGES * F_STAGE_BYTES + 512);  // [2 parity][2][128]
     int acc_stage = 0;
     uint32_t acc_phase = 0;
     const float kLog2e = 1.4426950408889634f;
-    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x) {
+    int it = 0;
+    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x, ++it) {
       const int row = tile * kTileM + rl;
       const bool valid = row < args.n;
       const bool live = valid && args.alive[row] != 0;
@@ -937,72 +942,88 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
       mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
       tc_fence_after();
       const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * TC_ACC_STRIDE;
-      // pass 1: e_i = exp(f_i + b_i), kept in TMEM in place; four partial sums
-      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll 1
-      for (int c0 = cbeg; c0 < cend; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(t + c0, v);
-        tmem_ld_wait();
+      // pass 1: e_i = exp(f_i + b_i), kept in TMEM in place; one sum per 16 columns
+      float cs[8];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float4 b = __ldg(reinterpret_cast<const float4 *>(args.b_fc + c0) + q);
-          const float bb[4] = {b.x, b.y, b.z, b.w};
-          float e[4];
+      for (int k = 0; k < 8; ++k) {
+        cs[k] = 0.0f;
+        const int c0 = cbeg + 16 * k;
+        if (c0 < cend) {
+          uint32_t v[16];
+          tmem_ld16(t + c0, v);
+          tmem_ld_wait();
+          float e[16];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float x = __uint_as_float(v[q * 4 + j]) + bb[j];
-            if (args.logits && valid) args.logits[(size_t)row * C + c0 + q * 4 + j] = live ? x : 0.0f;
-            e[j] = ex2_approx(x * kLog2e);
-            v[q * 4 + j] = __float_as_uint(e[j]);
+          for (int q = 0; q < 4; ++q) {
+            const float4 b = __ldg(reinterpret_cast<const float4 *>(args.b_fc + c0) + q);
+            const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float x = __uint_as_float(v[q * 4 + j]) + bb[j];
+              if (args.logits && valid) args.logits[(size_t)row * C + c0 + q * 4 + j] = live ? x : 0.0f;
+              e[q * 4 + j] = ex2_approx(x * kLog2e);
+              v[q * 4 + j] = __float_as_uint(e[q * 4 + j]);
+            }
           }
-          s0 += e[0]; s1 += e[1]; s2 += e[2]; s3 += e[3];
+          tmem_st16(t + c0, v);
+          cs[k] = (((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]))) +
+                  (((e[8] + e[9]) + (e[10] + e[11])) + ((e[12] + e[13]) + (e[14] + e[15])));
         }
-        tmem_st16(t + c0, v);
       }
       tmem_st_wait();
-      part_sum[half * kTileM + rl] = (s0 + s1) + (s2 + s3);
-      named_bar_sync(EPI_BAR_ID, F_EPI_WARPS * 32);
-      const float sum_lo = part_sum[rl], sum = sum_lo + part_sum[kTileM + rl];
-      // pass 2: first i with sum_{j<=i} p_j > r, p_j = e_j / sum (ref:322-333);
-      // the second half starts from the first half's share of the mass
-      const float inv = 1.0f / sum;
-      float psum = half == 0 ? 0.0f : sum_lo * inv;
-      int sel = -1;
-#pragma unroll 1
-      for (int c0 = cbeg; c0 < cend; c0 += 16) {
-        if (__all_sync(0xffffffffu, sel >= 0 || !live)) break;  // warp-uniform exit
-        uint32_t v[16];
-        tmem_ld16(t + c0, v);
-        tmem_ld_wait();
+      float my_sum = 0.0f;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          psum = fmaf(__uint_as_float(v[i]), inv, psum);
-          if (sel < 0 && psum > r) sel = c0 + i;
+      for (int k = 0; k < 8; ++k) my_sum += cs[k];
+      float *ps = part_sum + (it & 1) * 2 * kTileM;   // double-buffered: one barrier per tile is enough
+      ps[half * kTileM + rl] = my_sum;
+      named_bar_sync(EPI_BAR_ID, F_EPI_WARPS * 32);
+      const float sum_lo = ps[rl], tot = sum_lo + ps[kTileM + rl];
+      // first i with sum_{j<=i} e_j > r * sum (ref:322-333 on unnormalised mass,
+      // no max subtraction as in ref:302-313); if the mass never exceeds it the
+      // last character wins (ref:332)
+      const float rs = r * tot;
+      const bool fallback = !(tot > rs);
+      const int owner = fallback ? 1 : (sum_lo > rs ? 0 : 1);
+      const bool mine = live && owner == half;
+      int sel = (mine && fallback) ? C - 1 : -1;
+      float p = half == 0 ? 0.0f : sum_lo;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int c0 = cbeg + 16 * k;
+        if (c0 < cend) {
+          const bool need = mine && sel < 0 && (p + cs[k] > rs);
+          if (__any_sync(0xffffffffu, need)) {      // tcgen05.ld is warp-collective
+            uint32_t v[16];
+            tmem_ld16(t + c0, v);
+            tmem_ld_wait();
+            if (need) {
+              float q = p;
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                q += __uint_as_float(v[i]);
+                if (sel < 0 && q > rs) sel = c0 + i;
+              }
+              if (sel < 0) sel = c0 + 15;           // block sum crossed, running sum did not (rounding)
+            }
+          }
+          p += cs[k];
         }
       }
+      if (mine && sel < 0) sel = cend - 1;
       // accumulator drained: hand the TMEM stage back before the bookkeeping
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
-      if (half == 1) part_sel[rl] = sel;
-      named_bar_sync(EPI_BAR_ID, F_EPI_WARPS * 32);
-      if (half == 0 && valid) {
-        if (sel < 0) sel = part_sel[rl];
-        if (sel < 0) sel = C - 1;               // fallback n-1, ref:332
+      if (valid) {
         char *orow = args.output + (size_t)row * (args.T + 1);
-        if (args.step == 0)
+        if (args.step == 0 && half == 0)
           for (int l = 1; l <= args.T; ++l) orow[l] = 0;  // NUL pad, ref:643
-        if (live) {
+        if (mine) {
           orow[args.step] = (char)sel;  // EOS id is written too, ref:877
           args.chars[row] = sel;  // next step's layer-0 input: the row of the folded table it picks
           if (sel == args.eos) args.alive[row] = 0;  // ref:881
         }
       }
-      // part_sum / part_sel are rewritten next tile only after the first
-      // barrier of that tile's pass 1 ... which every thread reaches after
-      // having read them here; one more barrier keeps that airtight
-      named_bar_sync(EPI_BAR_ID, F_EPI_WARPS * 32);
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
   }
