@@ -401,6 +401,8 @@ def run_tp(args):
             "data": "synthetic (random-init weights of the named shape, uniform random floats)",
             "config": {"model": f"gru-namegen C256 E512 H{H} L2 T10", "global_batch": B, "seq_len": T,
                        "parallelism": f"tp{world}", "kernel_family": "tc",
+                       "allgather": ("nvswitch multicast (multimem.st / multimem.red)" if (tp is not None and tp.multicast)
+                                     else "unicast p2p stores" if tp is not None else "none"),
                        "l2": f"inputs larger than L2: {2 * 2 * B * H * 2 >> 20} MiB of hidden state + "
                              f"{3 * 3 * Hs * H * 2 >> 20} MiB of weights per rank streamed per character (no flush)",
                        "step": "one namegen() call on every rank: all names, all MAX_LEN characters"},

@@ -117,9 +117,13 @@ size_t b200gru_tp_shared_bytes(const b200gru_model *m) {
 }
 
 int b200gru_tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
+  return b200gru_tp_bind_mc(m, local_base, peer_bases, nullptr);
+}
+
+int b200gru_tp_bind_mc(b200gru_model *m, void *local_base, void *const *peer_bases, void *mc_base) {
   B200_REQUIRE(m && local_base && peer_bases, "null argument");
   DeviceGuard guard(m->device);
-  return tp_bind(m, local_base, peer_bases);
+  return tp_bind(m, local_base, peer_bases, mc_base);
 }
 
 int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,

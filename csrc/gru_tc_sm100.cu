@@ -103,6 +103,11 @@ struct LayerArgs {
   const uint32_t *wait_x, *wait_h;  // local counters [src][m_tile]
   __nv_bfloat16 *h_out_peer[8];     // h_out on every rank ([tp_rank] == h_out)
   uint32_t *signal_peer[8];         // this rank's counter row [m_tile] on every rank
+  // NVSwitch multicast views of the same two things (null: unicast to each peer).
+  // One store / one reduction leaves this GPU and the switch replicates it into
+  // every rank's copy: egress per tile drops from (world-1) copies to one.
+  __nv_bfloat16 *h_out_mc;
+  uint32_t *signal_mc;
 };
 
 // element offset of (row, col) in a panelled hidden buffer
@@ -260,8 +265,12 @@ __device__ __forceinline__ void epilogue_store_tile(const CUtensorMap *map_out, 
       const int r = idx >> 3, c = idx & 7;
       const uint4 v = *reinterpret_cast<const uint4 *>(stage_tile + r * 128 + ((c ^ (r & 7)) << 4));
       const size_t off = h_offset(m_tile * kTileM + r, col + c * 8, args.pw_log2, args.bpad);
-      for (int d = 0; d < args.tp_world; ++d)
-        if (d != args.tp_rank) *reinterpret_cast<uint4 *>(args.h_out_peer[d] + off) = v;
+      if (args.h_out_mc) {
+        multimem_st_v4(args.h_out_mc + off, v);   // one NVLink store, replicated by the switch
+      } else {
+        for (int d = 0; d < args.tp_world; ++d)
+          if (d != args.tp_rank) *reinterpret_cast<uint4 *>(args.h_out_peer[d] + off) = v;
+      }
     }
     // hand over to the publisher: slot (it & 1), reused every second tile
     const int slot = it & 1;
@@ -285,8 +294,12 @@ __device__ __forceinline__ void publish_tile(const LayerArgs &args, const PubRin
   const int m_tile = pub.m_tile[slot];
   mbar_arrive(&pub.empty[slot]);
   __threadfence_system();
-  for (int d = 0; d < args.tp_world; ++d)
-    red_release_sys_add(args.signal_peer[d] + m_tile, 1u);
+  if (args.signal_mc) {
+    multimem_red_release_sys_add(args.signal_mc + m_tile, 1u);  // bumps every rank's counter at once
+  } else {
+    for (int d = 0; d < args.tp_world; ++d)
+      red_release_sys_add(args.signal_peer[d] + m_tile, 1u);
+  }
 }
 
 // ------------------------------------------------------------ TMA producer
@@ -1176,7 +1189,7 @@ static int make_h_maps(b200gru_model *m) {
   return 0;
 }
 
-int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
+int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases, void *mc_base) {
   B200_REQUIRE(m->tp_world > 1, "model was not created for tensor parallelism");
   const int L = m->cfg.num_layers;
   const size_t hb = tp_h_bytes(m);
@@ -1193,6 +1206,13 @@ int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases) {
       }
     m->tp_sync[r] = reinterpret_cast<uint32_t *>(base + off_sync);
   }
+  m->tp_mc_base = static_cast<uint8_t *>(mc_base);
+  if (mc_base)
+    for (int l = 0; l < L; ++l)
+      for (int pp = 0; pp < 2; ++pp) {
+        m->tp_h_mc[l][pp] = reinterpret_cast<__nv_bfloat16 *>(m->tp_mc_base + (size_t)(l * 2 + pp) * hb);
+        m->tp_cnt_mc[l][pp] = reinterpret_cast<uint32_t *>(m->tp_mc_base + off_cnt + (size_t)(l * 2 + pp) * cb);
+      }
   for (int l = 0; l < L; ++l)
     for (int pp = 0; pp < 2; ++pp) m->tc[l].h[pp] = m->tp_h[m->tp_rank][l][pp];
   if (int rc = make_h_maps(m)) return rc;
@@ -1342,6 +1362,10 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
         for (int r = 0; r < W; ++r) {
           a.h_out_peer[r] = m->tp_h[r][l][wr];
           a.signal_peer[r] = m->tp_cnt[r][l][wr] + (size_t)R * mt_max;
+        }
+        if (m->tp_mc_base) {
+          a.h_out_mc = m->tp_h_mc[l][wr];
+          a.signal_mc = m->tp_cnt_mc[l][wr] + (size_t)R * mt_max;
         }
         a.wait_h = m->tp_cnt[R][l][rd];
         a.expect_h = m->tp_rounds[l][rd] * per_round;

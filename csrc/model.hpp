@@ -89,6 +89,9 @@ struct b200gru_model {
   __nv_bfloat16 *tp_h[8][B200GRU_MAX_LAYERS][2] = {};      // [rank][layer][pp] hidden buffers
   uint32_t *tp_cnt[8][B200GRU_MAX_LAYERS][2] = {};         // [rank][layer][pp] -> [src][m_tile]
   uint32_t *tp_sync[8] = {};                               // [rank] -> [src] call-fence words
+  uint8_t *tp_mc_base = nullptr;                           // NVSwitch multicast view of the shared region (optional)
+  __nv_bfloat16 *tp_h_mc[B200GRU_MAX_LAYERS][2] = {};
+  uint32_t *tp_cnt_mc[B200GRU_MAX_LAYERS][2] = {};
 
   // --- CUDA graphs: the 31 launches of a tensor-core generate are captured once
   // per (n, io) and replayed, which removes the per-launch CPU cost that
@@ -157,7 +160,7 @@ __global__ void tc_signal_done_kernel(uint32_t *flag, uint32_t value);
 int persist_prepare(b200gru_model *m);
 int persist_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s);
 size_t tp_shared_bytes(const b200gru_model *m);
-int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases);
+int tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases, void *mc_base);
 // TMA descriptor helper (tma_host.cu)
 int make_tmap_bf16_2d(CUtensorMap *map, const void *base, uint64_t rows,
                       uint64_t cols, uint32_t box_rows, uint32_t box_cols,

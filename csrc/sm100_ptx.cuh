@@ -406,6 +406,21 @@ __device__ __forceinline__ void red_release_gpu_add(uint32_t *p, uint32_t v) {
                : "memory");
 }
 
+// ------------------------------------------------ NVSwitch multicast (NVLS)
+// `mc` is an address in a multicast mapping (cuMulticast* object bound to the
+// same buffer on every GPU): ONE store leaves this GPU and the switch delivers
+// it to every GPU's copy, this one included.
+__device__ __forceinline__ void multimem_st_v4(void *mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+// one reduction that lands on every GPU's copy of the word; release: this
+// thread's earlier (fenced) stores are visible to whoever acquires the new value
+__device__ __forceinline__ void multimem_red_release_sys_add(uint32_t *mc, uint32_t v) {
+  asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+
 // atomic add that both acquires and releases at GPU scope; returns the old value
 __device__ __forceinline__ uint32_t atom_add_acq_rel_gpu(uint32_t *p, uint32_t v) {
   uint32_t old;

@@ -52,6 +52,7 @@ def _declare(lib):
         "b200gru_model_create_tp": (c_int, [cfg, c_void_p, c_int, c_int, c_int, c_int, P(c_void_p)]),
         "b200gru_tp_shared_bytes": (c_size_t, [c_void_p]),
         "b200gru_tp_bind": (c_int, [c_void_p, c_void_p, P(c_void_p)]),
+        "b200gru_tp_bind_mc": (c_int, [c_void_p, c_void_p, P(c_void_p), c_void_p]),
         "b200gru_model_destroy": (c_int, [c_void_p]),
         "b200gru_model_device_bytes": (c_int64, [c_void_p]),
         "b200gru_generate": (c_int, [c_void_p, c_int, c_int, P(CIo), c_void_p]),

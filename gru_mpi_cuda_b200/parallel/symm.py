@@ -75,3 +75,44 @@ class SymmBuffer:
             dist.barrier(group=self.group)
         self.lib.b200gru_symm_free(self.device, ctypes.c_void_p(self.local_ptr))
         self.local_ptr = None
+
+
+class McBuffer:
+    """Peer-visible buffer that also has an NVSwitch MULTICAST address.
+
+    Same role as `SymmBuffer` (one buffer per rank, every rank holds pointers
+    to all of them) plus `mc_ptr`: an address in a multicast mapping of all the
+    copies, so that a single `multimem.st` / `multimem.red` issued by a kernel
+    lands in every rank's buffer (NVLink SHARP).  CUDA IPC handles cannot carry
+    that, the memory has to come from `cuMemCreate` and be bound to a
+    `cuMulticast` object on every rank; torch's symmetric memory does exactly
+    this bootstrap (handle exchange over the process group), so it is used for
+    the plumbing only.  `mc_ptr` is 0 where the fabric has no multicast.
+    """
+
+    def __init__(self, nbytes: int, device: int, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.device = device
+        self.nbytes = int(nbytes)
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self._t = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=torch.device("cuda", device))
+        self._t.zero_()
+        self._hdl = symm_mem.rendezvous(self._t, self.group)
+        self.ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        self.local_ptr = self.ptrs[self.rank]
+        self.mc_ptr = int(self._hdl.multicast_ptr or 0)
+        self.local = self._t
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)
+
+    def close(self):
+        if self._t is None:
+            return
+        torch.cuda.synchronize(self.device)
+        if dist.is_initialized():
+            dist.barrier(group=self.group)
+        self._hdl = None
+        self._t = None
+        self.local = None

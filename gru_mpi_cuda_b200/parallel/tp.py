@@ -25,11 +25,16 @@ import torch.distributed as dist
 
 from .. import _native
 from ..models.namegen import NameGenerator
-from .symm import SymmBuffer
+import os
+
+from .symm import McBuffer, SymmBuffer
 
 
 class TPContext:
-    def __init__(self, cfg, params, device: int, max_batch: int, group=None):
+    def __init__(self, cfg, params, device: int, max_batch: int, group=None, multicast: bool | None = None):
+        """`multicast`: publish the hidden slices through the NVSwitch multicast
+        mapping (one store per 16 bytes instead of one per peer).  Default: on
+        when the fabric offers it (`B200GRU_TP_MC=0` turns it off for A/B runs)."""
         self.cfg = cfg
         self.device = device
         self.group = group
@@ -41,9 +46,28 @@ class TPContext:
         T = cfg.max_len
         self.max_batch = max_batch
         nbytes = self.lib.b200gru_tp_shared_bytes(self.gen._h)
-        self.shared = SymmBuffer(nbytes, device, group)
+        if multicast is None:
+            multicast = os.environ.get("B200GRU_TP_MC", "1") != "0"
+        self.shared = None
+        if multicast:
+            try:
+                self.shared = McBuffer(nbytes, device, group)
+            except Exception as e:  # noqa: BLE001  (no symmetric-memory support here: unicast P2P instead)
+                self.mc_error = repr(e)
+        # every rank must take the same route
+        ok = torch.tensor([1 if (self.shared is not None and self.shared.mc_ptr) else 0], device=torch.device("cuda", device))
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if multicast and not int(ok.item()):
+            if self.shared is not None:
+                self.shared.close()
+            self.shared = None
+        if self.shared is None:
+            self.shared = SymmBuffer(nbytes, device, group)
+        self.multicast = isinstance(self.shared, McBuffer)
         peers = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(p) for p in self.shared.ptrs])
-        _native.check(self.lib.b200gru_tp_bind(self.gen._h, ctypes.c_void_p(self.shared.local_ptr), peers), "tp_bind")
+        _native.check(self.lib.b200gru_tp_bind_mc(self.gen._h, ctypes.c_void_p(self.shared.local_ptr), peers,
+                                                   ctypes.c_void_p(self.shared.mc_ptr) if self.multicast else None),
+                      "tp_bind")
         # root-owned I/O, read / written in place by every rank's kernels (as in DP)
         # two halves, used alternately: a peer may still be reading call e's floats
         # (every rank's sampling kernels load them over NVLink) while the root

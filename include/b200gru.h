@@ -128,6 +128,16 @@ int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
 size_t b200gru_tp_shared_bytes(const b200gru_model *m);
 /* peer_bases[r] = mapped address of rank r's region (entry tp_rank ignored). */
 int b200gru_tp_bind(b200gru_model *m, void *local_base, void *const *peer_bases);
+/* Same, plus `mc_base`: the address of an NVSwitch multicast mapping
+ * (cuMulticastCreate / BindMem, e.g. torch symmetric memory's multicast_ptr) of
+ * the SAME region on all ranks.  With it the all-gather of a layer's new hidden
+ * slice is one multimem.st per 16 bytes (the switch replicates it into every
+ * rank's buffer) and one multimem.red per tile counter, instead of one store /
+ * reduction per peer: NVLink egress per call drops by (tp_world - 1)x.
+ * mc_base == NULL is b200gru_tp_bind.  The reference has no counterpart (every
+ * rank holds all weights, ref:370-407). */
+int b200gru_tp_bind_mc(b200gru_model *m, void *local_base, void *const *peer_bases,
+                       void *mc_base);
 /* namegen_finalize() equivalent (ref:897-1033). */
 int b200gru_model_destroy(b200gru_model *m);
 int64_t b200gru_model_device_bytes(const b200gru_model *m);

@@ -105,7 +105,7 @@ def run_tp(n_names: int, hidden: int):
         assert torch.equal(out, mine)
         # same bf16 math, same tiles; only the K-chunk order of the accumulation differs
         assert agree > 0.97, f"TP rows agree with single-GPU rows on only {agree:.3f}"
-        print(f"GPU_TP_OK world={world} hidden={hidden} n={n_names} agree={agree:.4f}")
+        print(f"GPU_TP_OK world={world} hidden={hidden} n={n_names} agree={agree:.4f} multicast={tp.multicast}")
     # every rank must have sampled exactly the same characters
     gathered = [None] * world
     dist.all_gather_object(gathered, mine.numpy().tobytes())

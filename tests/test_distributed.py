@@ -78,3 +78,16 @@ def test_tensor_parallel_matches_single_gpu(hidden, n):
     r = _torchrun(world, "tp", n, hidden, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "GPU_TP_OK" in r.stdout
+
+
+@pytest.mark.gpu
+def test_tensor_parallel_h8192_on_8_gpus():
+    """BASELINE.json config 4 at its real shape: hidden 8192 sharded over 8 GPUs
+    (1024 units per rank), small batch, against the single-GPU tensor-core path
+    on the same weights.  Batch sizes vary between calls and every call has its
+    own random floats (see dist_worker.run_tp)."""
+    if torch.cuda.device_count() < 8:
+        pytest.skip("needs 8 GPUs")
+    r = _torchrun(8, "tp", 300, 8192, timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "GPU_TP_OK world=8 hidden=8192" in r.stdout
