@@ -68,6 +68,21 @@ def run_gpu(n_names: int, method: str):
         dist.barrier()
         comm.close()
         gen.finalize()
+    # drop_remainder=False: the N % size names the reference silently drops
+    # (ref:628) go to the last rank instead, so every row is generated
+    if n_names % world and n_names >= world:
+        gen = NameGenerator(cfg, params, device=local, max_batch=n_names, mode="exact")
+        comm = DPContext(cfg, local, n_names, method="p2p", drop_remainder=False)
+        gen.comm = comm
+        out = gen.generate(n_names, rf if rank == 0 else None)
+        gen.comm = None
+        if rank == 0:
+            single = gen.generate(n_names, rf)
+            assert torch.equal(out, single), "drop_remainder=False: rows differ from the 1-rank run"
+            print(f"GPU_DP_KEEP_REMAINDER_OK world={world} n={n_names}")
+        dist.barrier()
+        comm.close()
+        gen.finalize()
     dist.destroy_process_group()
 
 

@@ -106,8 +106,9 @@ def test_default_shape_tc_vs_exact():
         ex = g.generate(n, r, mode="exact")
     want = oracle.generate(cfg, p, r, n_names=16)
     assert torch.equal(ex[:16], want)
-    assert (tc[:, 0] == ex[:, 0]).float().mean() > 0.97
-    assert (tc == ex).all(dim=1).float().mean() > 0.6
+    # bounds derived from the measured logit error, see tests/test_gpu_accuracy.py
+    assert (tc[:, 0] == ex[:, 0]).float().mean() > 0.99
+    assert (tc == ex).all(dim=1).float().mean() > 0.95
 
 
 def test_eos_stops_and_pads(tiny_cfg):

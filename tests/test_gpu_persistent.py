@@ -117,9 +117,9 @@ def test_persistent_default_shape_vs_exact():
         ex = g.generate(n, r, mode="exact")
         g.set_path("multi")
         ml = g.generate(n, r)
-    assert (tc[:, 0] == ex[:, 0]).float().mean() > 0.97
-    assert (tc == ex).all(dim=1).float().mean() > 0.6
-    assert (tc == ml).all(dim=1).float().mean() > 0.6
+    assert (tc[:, 0] == ex[:, 0]).float().mean() > 0.99
+    assert (tc == ex).all(dim=1).float().mean() > 0.95
+    assert (tc == ml).all(dim=1).float().mean() > 0.95
 
 
 @pytest.mark.parametrize("world", [2, 8])
