@@ -22,17 +22,7 @@ namespace {
 
 template <typename T>
 int dev_alloc(b200gru_model *m, T **out, size_t count) {
-  void *p = nullptr;
-  size_t bytes = count * sizeof(T);
-  if (bytes == 0) bytes = sizeof(T);
-  cudaError_t e = cudaMalloc(&p, bytes);
-  if (e != cudaSuccess)
-    return fail(B200GRU_ERR_CUDA, "cudaMalloc(%zu bytes) failed: %s", bytes,
-                cudaGetErrorString(e));
-  m->allocs.push_back(p);
-  m->device_bytes += (int64_t)bytes;
-  *out = static_cast<T *>(p);
-  return 0;
+  return model_alloc(m, out, count ? count : 1);
 }
 
 struct DeviceGuard {
@@ -51,11 +41,30 @@ struct DeviceGuard {
 __global__ void wait_flags_kernel(const uint32_t *flags, int n, uint32_t value) {
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     // epochs only grow: '>=' (wrap-safe) tolerates a peer that is already a call ahead
-    while ((int32_t)(sm100::ld_acquire_sys(flags + i) - value) < 0) __nanosleep(200);
+#ifdef B200GRU_DEBUG
+    sm100::SpinGuard g;
+#endif
+    uint32_t v;
+    while ((int32_t)((v = sm100::ld_acquire_sys(flags + i)) - value) < 0) {
+      __nanosleep(200);
+#ifdef B200GRU_DEBUG
+      g.tick("rank flag", flags + i, value, v);
+#endif
+    }
   }
   __syncthreads();
   __threadfence_system();
 }
+
+#ifdef B200GRU_DEBUG
+constexpr size_t kGuardBytes = 4096;
+constexpr unsigned char kGuardByte = 0xA5;
+__global__ void guard_check_kernel(const unsigned char *lo, const unsigned char *hi, size_t n,
+                                   unsigned int *bad) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    if (lo[i] != kGuardByte || hi[i] != kGuardByte) atomicAdd(bad, 1u);
+}
+#endif
 
 int create_impl(b200gru_model *m, const float *params_host) {
   const b200gru_config &c = m->cfg;
@@ -105,7 +114,73 @@ int create_impl(b200gru_model *m, const float *params_host) {
 
 }  // namespace
 
+namespace b200gru {
+
+int model_alloc_bytes(b200gru_model *m, void **out, size_t bytes) {
+  if (bytes == 0) bytes = 4;
+  void *p = nullptr;
+#ifdef B200GRU_DEBUG
+  const size_t body = (bytes + 255) / 256 * 256;
+  cudaError_t e = cudaMalloc(&p, body + 2 * kGuardBytes);
+#else
+  cudaError_t e = cudaMalloc(&p, bytes);
+#endif
+  if (e != cudaSuccess)
+    return fail(B200GRU_ERR_CUDA, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+  m->allocs.push_back(p);
+  m->device_bytes += (int64_t)bytes;
+#ifdef B200GRU_DEBUG
+  // [guard | body rounded to 256 | guard]: the rounding slack belongs to the
+  // upper guard's side and is patterned too
+  B200_CUDA(cudaMemset(p, kGuardByte, body + 2 * kGuardBytes));
+  p = static_cast<unsigned char *>(p) + kGuardBytes;
+  m->guarded.emplace_back(p, body);
+#endif
+  *out = p;
+  return 0;
+}
+
+int check_guards(b200gru_model *m, const char *when) {
+#ifdef B200GRU_DEBUG
+  unsigned int *bad = nullptr;
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMalloc(&bad, sizeof(unsigned int)));
+  for (size_t i = 0; i < m->guarded.size(); ++i) {
+    const unsigned char *body = static_cast<const unsigned char *>(m->guarded[i].first);
+    B200_CUDA(cudaMemset(bad, 0, sizeof(unsigned int)));
+    guard_check_kernel<<<8, 256>>>(body - kGuardBytes, body + m->guarded[i].second, kGuardBytes, bad);
+    unsigned int h = 0;
+    B200_CUDA(cudaMemcpy(&h, bad, sizeof(h), cudaMemcpyDeviceToHost));
+    if (h) {
+      cudaFree(bad);
+      return fail(B200GRU_ERR_STATE, "guard band of allocation #%zu (%zu bytes) damaged (%u bytes) %s",
+                  i, m->guarded[i].second, h, when);
+    }
+  }
+  cudaFree(bad);
+#else
+  (void)m; (void)when;
+#endif
+  return 0;
+}
+
+}  // namespace b200gru
+
 extern "C" {
+
+int b200gru_model_check(b200gru_model *m) {
+  B200_REQUIRE(m, "null model");
+  DeviceGuard guard(m->device);
+  return check_guards(m, "(b200gru_model_check)");
+}
+
+int b200gru_debug_build(void) {
+#ifdef B200GRU_DEBUG
+  return 1;
+#else
+  return 0;
+#endif
+}
 
 int b200gru_model_create(const b200gru_config *cfg, const float *params,
                          int device, int max_batch, b200gru_model **out) {
@@ -181,6 +256,7 @@ int b200gru_model_destroy(b200gru_model *m) {
   if (!m) return 0;
   DeviceGuard guard(m->device);
   cudaError_t first = cudaDeviceSynchronize();
+  const int guards_rc = check_guards(m, "at destroy");
   for (cudaEvent_t e : m->trace_ev) cudaEventDestroy(e);
   for (auto &g : m->graphs) {
     cudaGraphExecDestroy(g.exec);
@@ -195,15 +271,29 @@ int b200gru_model_destroy(b200gru_model *m) {
   delete m;
   if (first != cudaSuccess)
     return fail(B200GRU_ERR_CUDA, "destroy: %s", cudaGetErrorString(first));
-  return 0;
+  return guards_rc;
 }
 
 int64_t b200gru_model_device_bytes(const b200gru_model *m) {
   return m ? m->device_bytes : 0;
 }
 
+static int generate_impl(b200gru_model *m, int mode, int n, const b200gru_io *io, void *stream);
+
 int b200gru_generate(b200gru_model *m, int mode, int n, const b200gru_io *io,
                      void *stream) {
+  int rc = generate_impl(m, mode, n, io, stream);
+#ifdef B200GRU_DEBUG
+  // debug builds give up asynchrony: wait for the call and verify every guard band
+  if (rc == 0 && m && !(io && (io->done_flag || io->ready_flag)) && m->tp_world == 1) {
+    DeviceGuard guard(m->device);
+    rc = check_guards(m, "after generate");
+  }
+#endif
+  return rc;
+}
+
+static int generate_impl(b200gru_model *m, int mode, int n, const b200gru_io *io, void *stream) {
   B200_REQUIRE(m && io, "null argument");
   B200_REQUIRE(n >= 0 && n <= m->max_batch, "n=%d exceeds max_batch=%d", n,
                m->max_batch);

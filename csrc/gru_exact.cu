@@ -142,6 +142,7 @@ __global__ void exact_gates_kernel(const float *__restrict__ gi_table,
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (size_t)n * H) return;
   int b = (int)(idx / H), i = (int)(idx % H);
+  B200_DASSERT(!gi_table || chars[b] >= 0, "negative character id %d in row %d", gi_table ? chars[b] : 0, b);
   const float *gi = gi_table ? gi_table + (size_t)chars[b] * 3 * H
                              : gi_gemm + (size_t)b * 3 * H;
   const float *ghb = gh + (size_t)b * 3 * H;
@@ -193,6 +194,7 @@ __global__ void exact_sample_kernel(float *__restrict__ logits,
       break;
     }
   }
+  B200_DASSERT(sel >= 0 && sel < C && step < T, "sampled character %d of %d at step %d of %d", sel, C, step, T);
   row[step] = (char)sel;
   chars[b] = sel;
   if (sel == eos) alive[b] = 0;

@@ -301,6 +301,10 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
               if (kb == 0) tl.stamp((step << 8) | (l << 4) | TL_MMA_START);
               if (elect_one()) {
                 const uint64_t da = desc_ring + (uint64_t)((stage * PS_A_BYTES) >> 4);
+                B200_DASSERT(stage < S && acc_stage < PS_ACC_STAGES &&
+                                 (kb < kb_h ? a.off_hh[l] + (kb + 1) * PS_KB_BYTES
+                                            : a.off_ih[l] + (kb - kb_h + 1) * PS_KB_BYTES) <= a.w_bytes,
+                             "resident weight block / ring stage out of range (layer %d k-block %d)", l, kb);
                 if (kb < kb_h) {  // [r | z | n_h] += h . W_hh^T
                   const uint64_t db = desc_w + (uint64_t)((a.off_hh[l] + kb * PS_KB_BYTES) >> 4);
                   umma_bf16_2sm(d + 16, da, db, idesc, 1u);
@@ -372,6 +376,7 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
               tl.stamp((step << 8) | (l << 4) | TL_CHARS_READY);
               if (row < a.n) c = __ldcg(a.chars + row);
             }
+            B200_DASSERT(c >= 0 && c < a.C, "layer-0 table row %d of %d", c, a.C);
             const uint4 *trow = reinterpret_cast<const uint4 *>(
                 a.t0p + ((size_t)pair * a.C + c) * (3 * PS_UNITS) + half * 8);
             const uint4 tn = __ldg(trow), tr = __ldg(trow + 2), tz = __ldg(trow + 4);
@@ -424,6 +429,8 @@ __device__ __forceinline__ void persist_main(const PersistMaps &maps, const Pers
             __nv_bfloat162 p = __floats2bfloat162_rn(hn2[0], hn2[1]);
             packed[i >> 1] = *reinterpret_cast<uint32_t *>(&p);
           }
+          B200_DASSERT(row < a.mt_max * kTileM && unit0 + 8 <= a.H && acc_stage < PS_ACC_STAGES,
+                       "h' store row %d unit %d / accumulator stage %d out of range", row, unit0, acc_stage);
           *reinterpret_cast<uint4 *>(a.h[l][wr] + (size_t)row * a.H + unit0) =
               make_uint4(packed[0], packed[1], packed[2], packed[3]);
           // publish: this CTA's slice of (layer, buffer, tile) is in place
@@ -698,6 +705,8 @@ __device__ __forceinline__ void persist_fc(const PersistMaps &maps, const Persis
         if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
         bool still = false;
         char *orow = a.output + (size_t)row * (a.T + 1);
+        B200_DASSERT(!mine || (sel >= 0 && sel < C && row < a.n), "sampled character %d of %d, row %d of %d", sel, C,
+                     row, a.n);
         if (mine) {
           a.chars[row] = sel;
           still = sel != a.eos;                     // ref:881
@@ -788,15 +797,7 @@ static size_t ps_sync_words(const b200gru_model *m) {
 
 template <typename T>
 static int ps_alloc(b200gru_model *m, T **out, size_t count) {
-  void *p = nullptr;
-  const size_t bytes = count * sizeof(T);
-  cudaError_t e = cudaMalloc(&p, bytes);
-  if (e != cudaSuccess)
-    return fail(B200GRU_ERR_CUDA, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
-  m->allocs.push_back(p);
-  m->device_bytes += (int64_t)bytes;
-  *out = static_cast<T *>(p);
-  return 0;
+  return model_alloc(m, out, count);
 }
 
 // Decides whether the persistent kernel can run this model on this GPU and, if

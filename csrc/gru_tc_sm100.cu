@@ -80,6 +80,7 @@ struct LayerArgs {
   // 450-600 GB/s); wide panels spread a TMA box over more L2 slices.
   int pw_log2;      // log2(panel width in elements)
   int bpad;         // rows per panel
+  int h_full;       // full hidden width H (element extent of a hidden buffer = bpad * H; debug checks)
   // layer 0 only: the folded input table, [H/64][C][2 halves][2 chunks][n|r|z][16] bf16,
   // and the current character of every name
   const __nv_bfloat16 *t0q;
@@ -124,7 +125,16 @@ __device__ __forceinline__ void h_coords(int row, int col, int pw_log2, int bpad
 
 // All lanes poll (one coalesced request); every lane has then acquired.
 __device__ __forceinline__ void tp_wait_counter(const uint32_t *p, uint32_t expect) {
+#ifdef B200GRU_DEBUG
+  SpinGuard g;
+  uint32_t v;
+  while ((int32_t)((v = ld_acquire_sys(p)) - expect) < 0) {
+    __nanosleep(64);
+    g.tick("tensor-parallel tile counter", p, expect, v);
+  }
+#else
   while ((int32_t)(ld_acquire_sys(p) - expect) < 0) __nanosleep(64);
+#endif
 }
 
 // 32-byte read-only global load (one request instead of two 16-byte ones: the
@@ -265,6 +275,8 @@ __device__ __forceinline__ void epilogue_store_tile(const CUtensorMap *map_out, 
       const int r = idx >> 3, c = idx & 7;
       const uint4 v = *reinterpret_cast<const uint4 *>(stage_tile + r * 128 + ((c ^ (r & 7)) << 4));
       const size_t off = h_offset(m_tile * kTileM + r, col + c * 8, args.pw_log2, args.bpad);
+      B200_DASSERT(off + 8 <= (size_t)args.bpad * args.h_full, "peer store offset %llu beyond hidden buffer (%d x %d)",
+                   (unsigned long long)off, args.bpad, args.h_full);
       if (args.h_out_mc) {
         multimem_st_v4(args.h_out_mc + off, v);   // one NVLink store, replicated by the switch
       } else {
@@ -340,6 +352,7 @@ __device__ __forceinline__ void produce_part(const CUtensorMap *map_a, const CUt
       co += (kw >> args.pw_log2) * args.bpad;
     }
     for (int jj = 0; jj < chunk_len; ++jj) {
+      B200_DASSERT(ring.stage >= 0 && ring.stage < STAGES, "smem ring stage %d of %d", ring.stage, STAGES);
       mbar_wait_relaxed(&empty_bar[ring.stage], ring.phase ^ 1, kProdSleepNs);
       if (elect_one()) {
         uint8_t *sa = smem + ring.stage * STAGE_BYTES;
@@ -464,6 +477,8 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
+      B200_DASSERT((d & 0xffffu) + 256 <= (tmem_base & 0xffffu) + TC_TMEM_COLS && acc_stage < 2 && stage < L_STAGES,
+                   "accumulator stage %d / smem stage %d out of range", acc_stage, stage);
       for (int kb = 0; kb < kb_total; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
@@ -528,11 +543,17 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       if (tile_q >= total_tiles) return;
       const int mq = tile_q / args.n_blocks, nq = tile_q % args.n_blocks;
       if (has_h) {
+        B200_DASSERT(h_offset(mq * kTileM + r, args.col0 + nq * 64 + half * 32, args.pw_log2, args.bpad) + 32 <=
+                         (size_t)args.bpad * args.h_full,
+                     "h_prev offset beyond hidden buffer (tile %d)", tile_q);
         const uint4 *src = reinterpret_cast<const uint4 *>(
             args.h_prev + h_offset(mq * kTileM + r, args.col0 + nq * 64 + half * 32, args.pw_log2, args.bpad));
 #pragma unroll
         for (int i = 0; i < 4; ++i) hq[i] = src[i];
       }
+      B200_DASSERT(!LAYER0 || (c >= 0 && c < args.num_char && nq < args.n_blocks),
+                   "layer-0 table row out of range: char %d of %d, unit block %d of %d", c, args.num_char, nq,
+                   args.n_blocks);
       if (LAYER0) load_t0_rows(args.t0q + (((size_t)nq * args.num_char + c) * 2 + half) * 96, tq);
     };
 #pragma unroll
@@ -697,6 +718,8 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
         mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
+        B200_DASSERT((d & 0xffffu) + 256 <= (tmem_base & 0xffffu) + TC_TMEM_COLS && acc_stage < 2 && stage < P_STAGES,
+                     "accumulator stage %d / smem stage %d out of range", acc_stage, stage);
         for (int kb = 0; kb < kb_total; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -755,11 +778,17 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       if (tile_q >= total_tiles) return;
       const int mq = (tile_q / args.n_blocks) * 2 + (int)rank, nq = tile_q % args.n_blocks;
       if (has_h) {
+        B200_DASSERT(h_offset(mq * kTileM + r, args.col0 + nq * 64 + half * 32, args.pw_log2, args.bpad) + 32 <=
+                         (size_t)args.bpad * args.h_full,
+                     "h_prev offset beyond hidden buffer (tile %d)", tile_q);
         const uint4 *src = reinterpret_cast<const uint4 *>(
             args.h_prev + h_offset(mq * kTileM + r, args.col0 + nq * 64 + half * 32, args.pw_log2, args.bpad));
 #pragma unroll
         for (int i = 0; i < 4; ++i) hq[i] = src[i];
       }
+      B200_DASSERT(!LAYER0 || (c >= 0 && c < args.num_char && nq < args.n_blocks),
+                   "layer-0 table row out of range: char %d of %d, unit block %d of %d", c, args.num_char, nq,
+                   args.n_blocks);
       if (LAYER0) load_t0_rows(args.t0q + (((size_t)nq * args.num_char + c) * 2 + half) * 96, tq);
     };
 #pragma unroll
@@ -1031,6 +1060,8 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
         char *orow = args.output + (size_t)row * (args.T + 1);
         if (args.step == 0 && half == 0)
           for (int l = 1; l <= args.T; ++l) orow[l] = 0;  // NUL pad, ref:643
+        B200_DASSERT(!mine || (sel >= 0 && sel < C && row < args.n && args.step < args.T),
+                     "sampled character %d of %d, row %d of %d, step %d of %d", sel, C, row, args.n, args.step, args.T);
         if (mine) {
           orow[args.step] = (char)sel;  // EOS id is written too, ref:877
           args.chars[row] = sel;  // next step's layer-0 input: the row of the folded table it picks
@@ -1133,8 +1164,18 @@ __global__ void tc_signal_done_kernel(uint32_t *flag, uint32_t value) {
 // `epoch` (its kernels no longer read or write our buffers).  signal: tell
 // every peer that we have.
 __global__ void tp_wait_epoch_kernel(const uint32_t *sync_local, int world, uint32_t epoch) {
-  if ((int)threadIdx.x < world)
-    while ((int32_t)(ld_acquire_sys(sync_local + threadIdx.x) - epoch) < 0) __nanosleep(200);
+  if ((int)threadIdx.x < world) {
+#ifdef B200GRU_DEBUG
+    SpinGuard g;
+#endif
+    uint32_t v;
+    while ((int32_t)((v = ld_acquire_sys(sync_local + threadIdx.x)) - epoch) < 0) {
+      __nanosleep(200);
+#ifdef B200GRU_DEBUG
+      g.tick("tensor-parallel call fence", sync_local + threadIdx.x, epoch, v);
+#endif
+    }
+  }
 }
 struct TpPeers { uint32_t *p[8]; };
 __global__ void tp_signal_epoch_kernel(TpPeers sync_slot, int world, uint32_t epoch) {
@@ -1146,16 +1187,7 @@ __global__ void tp_signal_epoch_kernel(TpPeers sync_slot, int world, uint32_t ep
 
 template <typename T>
 static int tc_alloc(b200gru_model *m, T **out, size_t count) {
-  void *p = nullptr;
-  size_t bytes = count * sizeof(T);
-  cudaError_t e = cudaMalloc(&p, bytes);
-  if (e != cudaSuccess)
-    return fail(B200GRU_ERR_CUDA, "cudaMalloc(%zu bytes) failed: %s", bytes,
-                cudaGetErrorString(e));
-  m->allocs.push_back(p);
-  m->device_bytes += (int64_t)bytes;
-  *out = static_cast<T *>(p);
-  return 0;
+  return model_alloc(m, out, count);
 }
 
 // Layout of the peer-visible region a tensor-parallel rank exposes:
@@ -1353,7 +1385,7 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
       a.kb_x = l == 0 ? 0 : H / TC_BLOCK_K;  // layer 0: table gather in the epilogue, no x-part GEMM
       if (l == 0) { a.t0q = m->t0q; a.chars = m->chars; a.num_char = C; }
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
-      a.pw_log2 = m->pw_log2; a.bpad = m->bpad; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
+      a.pw_log2 = m->pw_log2; a.bpad = m->bpad; a.h_full = H; a.bias = t.bias; a.h_prev = t.h[rd]; a.h_out = t.h[wr];
       a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.x_full = l > 0;
       a.col0 = R * Hs; a.flag_stride = mt_max;
       a.h_out_peer[0] = t.h[wr];

@@ -8,6 +8,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <utility>
 #include <vector>
 
 #include "errors.hpp"
@@ -39,6 +40,9 @@ struct b200gru_model {
   bool tc_ok = false;
   std::vector<b200gru::TensorSpec> lay;
   std::vector<void *> allocs;
+  // B200GRU_DEBUG builds: every allocation sits between two 4 KB guard bands
+  // filled with a pattern; (user pointer, bytes) of each is kept for the checks
+  std::vector<std::pair<void *, size_t>> guarded;
   int64_t device_bytes = 0;
   int last_launches = 0;
 
@@ -143,6 +147,19 @@ struct b200gru_model {
 };
 
 namespace b200gru {
+// Device allocation owned by the model (engine.cu).  In B200GRU_DEBUG builds the
+// block is surrounded by guard bands that check_guards() verifies.
+int model_alloc_bytes(b200gru_model *m, void **out, size_t bytes);
+template <typename T>
+inline int model_alloc(b200gru_model *m, T **out, size_t count) {
+  void *p = nullptr;
+  if (int rc = model_alloc_bytes(m, &p, count * sizeof(T))) return rc;
+  *out = static_cast<T *>(p);
+  return 0;
+}
+// Debug builds: 0 if every guard band of the model still holds its pattern, else
+// an error naming the damaged block (synchronises the device).  Release: 0.
+int check_guards(b200gru_model *m, const char *when);
 // exact path (gru_exact.cu)
 int exact_sgemm_tn(const float *a, const float *w, float *c, int m, int n,
                    int k, cudaStream_t s);

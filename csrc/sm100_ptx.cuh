@@ -10,7 +10,54 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdio>
+
+// ---- B200GRU_DEBUG: what stands in for compute-sanitizer on a pool where it is
+// closed.  Device-side assertions on computed offsets / ring indices / TMEM
+// columns, and every spin loop bounded by a wall-clock deadline so that a lost
+// signal is a trap with a message instead of a hang.
+#ifdef B200GRU_DEBUG
+#define B200_DASSERT(cond, ...)                                                          \
+  do {                                                                                   \
+    if (!(cond)) {                                                                       \
+      printf("b200gru debug assert (%s:%d, block %d thread %d): ", __FILE__, __LINE__,   \
+             (int)blockIdx.x, (int)threadIdx.x);                                         \
+      printf(__VA_ARGS__);                                                               \
+      printf("\n");                                                                     \
+      __trap();                                                                          \
+    }                                                                                    \
+  } while (0)
+#else
+#define B200_DASSERT(cond, ...) \
+  do {                          \
+  } while (0)
+#endif
+
 namespace sm100 {
+
+#ifdef B200GRU_DEBUG
+constexpr unsigned long long kSpinDeadlineNs = 20ull * 1000 * 1000 * 1000;  // 20 s
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// call once per failed poll; traps when the wait has lasted longer than the deadline
+struct SpinGuard {
+  unsigned long long t0 = 0;
+  uint32_t polls = 0;
+  __device__ __forceinline__ void tick(const char *what, const void *addr, uint32_t want, uint32_t seen) {
+    if ((++polls & 1023u) != 0) return;
+    const unsigned long long now = global_ns();
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > kSpinDeadlineNs) {
+      printf("b200gru debug: block %d thread %d waited > 20 s on %s %p (want %u, saw %u)\n", (int)blockIdx.x,
+             (int)threadIdx.x, what, addr, want, seen);
+      __trap();
+    }
+  }
+};
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
   return (uint32_t)__cvta_generic_to_shared(p);
@@ -73,8 +120,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
   return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+#ifdef B200GRU_DEBUG
+  SpinGuard g;
+  while (!mbar_try_wait(bar, parity)) g.tick("mbarrier", bar, parity, 0);
+#else
   while (!mbar_try_wait(bar, parity)) {
   }
+#endif
 }
 
 // Wait with a back-off between probes: for roles that have slack (epilogue
@@ -82,7 +134,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 // A bare try_wait loop re-issues every ~60 cycles; eight epilogue warps doing
 // that are half of a kernel's issued instructions, all of it spent spinning.
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity, uint32_t ns) {
+#ifdef B200GRU_DEBUG
+  SpinGuard g;
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(ns);
+    g.tick("mbarrier", bar, parity, 0);
+  }
+#else
   while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+#endif
 }
 
 // sub-block barrier over `nthreads` threads (bar.sync id, n)

@@ -18,11 +18,15 @@ ROOT = Path(__file__).resolve().parent.parent
 CSRC = ROOT / "csrc"
 LIB_DIR = Path(__file__).resolve().parent / "lib"
 OBJ_DIR = ROOT / "build" / "obj"
-LIB_PATH = LIB_DIR / "libb200gru.so"
+# B200GRU_DEBUG=1 selects the checking build (device assertions, guard bands,
+# bounded spin loops; see include/b200gru.h): a second library next to the
+# release one, so both can travel to the GPU box together.
+DEBUG = os.environ.get("B200GRU_DEBUG") == "1"
+LIB_PATH = LIB_DIR / ("libb200gru_debug.so" if DEBUG else "libb200gru.so")
 
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-ffp-contract=off,-Wall",
-          "-I", str(ROOT / "include")]
+          "-I", str(ROOT / "include")] + (["-DB200GRU_DEBUG"] if DEBUG else [])
 # fmad stays ON globally (tensor-core epilogues want it); the exact kernel uses
 # explicit __fmaf_rn/__fmul_rn/__fadd_rn so contraction cannot change it.
 CU_FLAGS = ["--expt-relaxed-constexpr", "-Xptxas", "-v"]

@@ -138,6 +138,11 @@ class NameGenerator:
         code = {"auto": 0, "multi": 1, "persistent": 2}[path]
         return bool(_native.check(self._lib.b200gru_model_set_path(self._h, code, persist_max_names), "set_path"))
 
+    def check(self) -> None:
+        """Debug build (`B200GRU_DEBUG=1`): verify the guard bands around every
+        device buffer of the model now; raises on damage.  No-op in release."""
+        _native.check(self._lib.b200gru_model_check(self._h), "model_check")
+
     def set_trace(self, on: bool = True) -> None:
         """Record a CUDA event after every launch of the tensor-core path."""
         _native.check(self._lib.b200gru_model_set_trace(self._h, 1 if on else 0))

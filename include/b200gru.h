@@ -192,6 +192,20 @@ int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
  * Environment: B200GRU_PATH, B200GRU_PERSIST_MAX set the defaults at create. */
 int b200gru_model_set_path(b200gru_model *m, int path, int persist_max_names);
 
+/* Debug build (libb200gru_debug.so, compiled with -DB200GRU_DEBUG; selected by
+ * B200GRU_DEBUG=1 in the Python package).  It stands in for compute-sanitizer,
+ * which this GPU pool does not allow: device-side assertions on computed global
+ * offsets, shared-memory ring / TMEM stage indices and sampled ids; every model
+ * allocation between two 4 KB guard bands that are verified after each
+ * single-rank generate (which therefore synchronises), by b200gru_model_check and
+ * at destroy; every spin loop (mbarrier, rank flags, tensor-parallel counters)
+ * bounded by a 20 s deadline that traps with a message.  The reference's own bugs
+ * of this kind: ref:294-300 (race), ref:1017 (cudaFree of a host pointer).
+ * b200gru_debug_build() is 1 in that library, 0 in the release one;
+ * b200gru_model_check() verifies the guard bands now (always 0 in release). */
+int b200gru_debug_build(void);
+int b200gru_model_check(b200gru_model *m);
+
 /* Tracing (absent in the reference): with set_trace(m, 1) the tensor-core
  * generate records a CUDA event after every launch; get_trace returns the
  * per-launch device times of the last call (synchronises on its last event). */
