@@ -227,6 +227,7 @@ int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
     // kernel path for tensor-core mode: auto picks the persistent kernel for small batches
     if (const char *e = getenv("B200GRU_PATH")) m->ps_path = atoi(e);
     if (const char *e = getenv("B200GRU_PERSIST_MAX")) m->ps_max_n = atoi(e);
+    if (const char *e = getenv("B200GRU_COMPACT")) m->compact = e[0] != '0';
   }
   {
     const char *e = getenv("B200GRU_TP_FAKE");
@@ -457,6 +458,21 @@ int b200gru_model_set_path(b200gru_model *m, int path, int persist_max_names) {
   m->ps_path = path;
   if (persist_max_names >= 0) m->ps_max_n = persist_max_names;
   return m->ps_ok ? 1 : 0;
+}
+
+int b200gru_model_set_compaction(b200gru_model *m, int on) {
+  B200_REQUIRE(m, "null model");
+  if (m->compact != (on != 0)) {
+    // captured graphs have the choice baked in
+    for (auto &g : m->graphs) {
+      cudaGraphExecDestroy(g.exec);
+      if (g.exec_tail) cudaGraphExecDestroy(g.exec_tail);
+      if (g.graph) cudaGraphDestroy(g.graph);
+    }
+    m->graphs.clear();
+  }
+  m->compact = on != 0;
+  return 0;
 }
 
 int b200gru_model_set_trace(b200gru_model *m, int on) {

@@ -69,6 +69,10 @@ constexpr int EPI_BAR_ID = 1;                 // named barrier of the epilogue w
 
 struct LayerArgs {
   int n;            // valid names (rows)
+  // Names that have hit EOS are compacted away between steps (ref:881-882 stops
+  // a name there): when non-null, the number of rows still in use is read from
+  // device memory at kernel start and replaces n / m_tiles.
+  const int *n_dev;
   int m_tiles;      // ceil(n / 128)
   int n_blocks;     // H / 64
   int kb_x;         // k-blocks (of 64) of the x operand
@@ -400,7 +404,6 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_tiles = args.m_tiles * args.n_blocks;
   const int kb_total = args.kb_x + args.kb_h;
 
   if (warp == 0 && lane == 0) {
@@ -450,6 +453,9 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
   // global data written by earlier kernels is read.
   pdl_launch_dependents();
   pdl_wait();
+  // rows in use: fixed for the call, or what the last compaction left
+  const int n_rows = args.n_dev ? __ldcg(args.n_dev) : args.n;
+  const int total_tiles = ((n_rows + kTileM - 1) / kTileM) * args.n_blocks;
 
   if (warp == 0) {
     // ===================================================== TMA producer
@@ -537,7 +543,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
     auto char_of = [&](int tile_q) -> int {
       if (!LAYER0 || tile_q >= total_tiles) return 0;
       const int row_q = (tile_q / args.n_blocks) * kTileM + r;
-      return row_q < args.n ? args.chars[row_q] : 0;
+      return row_q < n_rows ? args.chars[row_q] : 0;
     };
     auto request = [&](int tile_q, int c) {
       if (tile_q >= total_tiles) return;
@@ -643,8 +649,6 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
   const bool leader = rank == 0;
   const int pair = blockIdx.x >> 1;
   const int num_pairs = gridDim.x >> 1;
-  const int m2_tiles = (args.m_tiles + 1) >> 1;    // 256-name tiles
-  const int total_tiles = m2_tiles * args.n_blocks;
   const int kb_total = args.kb_x + args.kb_h;
 
   if (warp == 0 && lane == 0) {
@@ -689,6 +693,9 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
   tc_fence_after();
   pdl_launch_dependents();
   pdl_wait();  // see gru_layer_kernel
+  const int n_rows = args.n_dev ? __ldcg(args.n_dev) : args.n;
+  const int m2_tiles = (n_rows + 2 * kTileM - 1) / (2 * kTileM);    // 256-name tiles
+  const int total_tiles = m2_tiles * args.n_blocks;
 
   if (warp == 0) {
     // ============================ TMA producer (both CTAs, own smem)
@@ -772,7 +779,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
     auto char_of = [&](int tile_q) -> int {
       if (!LAYER0 || tile_q >= total_tiles) return 0;
       const int row_q = ((tile_q / args.n_blocks) * 2 + (int)rank) * kTileM + r;
-      return row_q < args.n ? args.chars[row_q] : 0;
+      return row_q < n_rows ? args.chars[row_q] : 0;
     };
     auto request = [&](int tile_q, int c) {
       if (tile_q >= total_tiles) return;
@@ -849,6 +856,9 @@ constexpr int F_SMEM_BYTES = 1024 + F_STAGES * F_STAGE_BYTES + 4096;
 
 struct FcArgs {
   int n, m_tiles, kb, H, C, T, step, eos;
+  const int *n_dev;         // rows in use after compaction (null: n)
+  const int32_t *slot_row;  // original name of every row (null: identity); rfloats / output are indexed by it
+  int *gone;                // optional: += names that hit EOS in this step (lets the compaction planner exit early)
   const float *b_fc;
   float *logits;            // optional [bpad, C] tap (tests / debugging)
   const float *rfloats;     // [n, T]   (may be a peer address)
@@ -889,6 +899,8 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
   const uint32_t tmem_base = *tmem_slot;
   pdl_launch_dependents();
   pdl_wait();  // prologue above may overlap the previous kernel's tail
+  const int n_rows = args.n_dev ? __ldcg(args.n_dev) : args.n;
+  const int m_tiles = (n_rows + kTileM - 1) / kTileM;
 
   if (warp == 0) {
     // TMA producer: warp-converged, one elected lane issues (see produce_part)
@@ -898,7 +910,7 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
     const int nchunks = tp ? args.tp_world : 1;
     const int chunk_len = tp ? args.kb_rank : args.kb;
     const int pw = 1 << args.pw_log2;
-    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x)
+    for (int tile = blockIdx.x; tile < m_tiles; tile += gridDim.x)
       for (int c = 0; c < nchunks; ++c) {
         int src = args.tp_rank + c;
         if (src >= args.tp_world) src -= args.tp_world;
@@ -933,7 +945,7 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
     uint32_t phase = 0, acc_phase = 0;
     const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)C);
     const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
-    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x) {
+    for (int tile = blockIdx.x; tile < m_tiles; tile += gridDim.x) {
       mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d = tmem_base + acc_stage * TC_ACC_STRIDE;
@@ -974,13 +986,15 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
     uint32_t acc_phase = 0;
     const float kLog2e = 1.4426950408889634f;
     int it = 0;
-    for (int tile = blockIdx.x; tile < args.m_tiles; tile += gridDim.x, ++it) {
+    for (int tile = blockIdx.x; tile < m_tiles; tile += gridDim.x, ++it) {
       const int row = tile * kTileM + rl;
-      const bool valid = row < args.n;
+      const bool valid = row < n_rows;
       const bool live = valid && args.alive[row] != 0;
+      // the name this row holds (rows are compacted as names finish)
+      const int name = (valid && args.slot_row) ? args.slot_row[row] : row;
       // this step's random float: fetched (possibly over NVLink from the root
       // rank's buffer — the MPI_Scatter of ref:636) before the accumulator wait
-      const float r = live ? args.rfloats[(size_t)row * args.T + args.step] : 2.0f;
+      const float r = live ? args.rfloats[(size_t)name * args.T + args.step] : 2.0f;
       mbar_wait_relaxed(&tmem_full[acc_stage], acc_phase, kEpiSleepNs);
       tc_fence_after();
       const uint32_t t = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_stage * TC_ACC_STRIDE;
@@ -1057,16 +1071,20 @@ fc_sample_kernel(const __grid_constant__ CUtensorMap map_h,
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
       if (valid) {
-        char *orow = args.output + (size_t)row * (args.T + 1);
+        char *orow = args.output + (size_t)name * (args.T + 1);
         if (args.step == 0 && half == 0)
           for (int l = 1; l <= args.T; ++l) orow[l] = 0;  // NUL pad, ref:643
-        B200_DASSERT(!mine || (sel >= 0 && sel < C && row < args.n && args.step < args.T),
-                     "sampled character %d of %d, row %d of %d, step %d of %d", sel, C, row, args.n, args.step, args.T);
+        B200_DASSERT(!mine || (sel >= 0 && sel < C && name >= 0 && name < args.n && args.step < args.T),
+                     "sampled character %d of %d, name %d of %d, step %d of %d", sel, C, name, args.n, args.step, args.T);
         if (mine) {
           orow[args.step] = (char)sel;  // EOS id is written too, ref:877
           args.chars[row] = sel;  // next step's layer-0 input: the row of the folded table it picks
           if (sel == args.eos) args.alive[row] = 0;  // ref:881
         }
+      }
+      if (args.gone) {
+        const unsigned ended = __ballot_sync(0xffffffffu, mine && sel == args.eos);
+        if (lane == 0 && ended) atomicAdd(args.gone, __popc(ended));
       }
       if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
     }
@@ -1147,12 +1165,15 @@ __global__ void pack_bias_kernel(const float *__restrict__ b_ih,
 }
 
 // Per-call reset: chars = SOS (ref:652), alive flags.
-__global__ void tc_init_kernel(int32_t *chars, uint8_t *alive, int n, int rows, int sos) {
+__global__ void tc_init_kernel(int32_t *chars, uint8_t *alive, int32_t *slot_row, int *state, int n, int rows,
+                               int sos) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx < rows) {
     chars[idx] = sos;
     alive[idx] = idx < n;
+    slot_row[idx] = idx;   // row i holds name i until the first compaction
   }
+  if (idx == 0) { state[0] = n; state[1] = n; state[2] = 0; state[3] = 0; }
 }
 
 __global__ void tc_signal_done_kernel(uint32_t *flag, uint32_t value) {
@@ -1182,6 +1203,113 @@ __global__ void tp_signal_epoch_kernel(TpPeers sync_slot, int world, uint32_t ep
   if ((int)threadIdx.x < world) {
     __threadfence_system();
     st_release_sys(sync_slot.p[threadIdx.x], epoch);
+  }
+}
+
+// ------------------------------------------------------------- compaction
+// The reference stops a name at EOS (ref:881-882).  Batched, a finished name
+// would keep occupying a GEMM row for the rest of the call, so a few times per
+// call the rows still running are packed to the front: three small launches
+// that do nothing unless at least one 256-name tile can be dropped.
+//   state[0] = rows in use (read by every later kernel), [1] = rows after the
+//   compaction being planned, [2] = whether it is carried out.
+__global__ void __launch_bounds__(1024, 1)
+compact_plan_kernel(const uint8_t *__restrict__ alive, int32_t *__restrict__ new_idx, int *state) {
+  __shared__ int warp_tot[32];
+  __shared__ int running;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int n = state[0];
+  {
+    // Cheap exit: the FC kernels count the names that ended since the last
+    // compaction (state[3]).  Packing moves every surviving row twice, so it is
+    // only worth it when at least 1/16 of the 256-name tiles (and at least one)
+    // can be dropped.
+    const int tiles = (n + 2 * kTileM - 1) / (2 * kTileM);
+    const int tiles_new = (n - state[3] + 2 * kTileM - 1) / (2 * kTileM);
+    const int need = tiles / 16 > 1 ? tiles / 16 : 1;
+    if (tiles - tiles_new < need) {
+      if (tid == 0) state[2] = 0;
+      return;
+    }
+  }
+  if (tid == 0) running = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += 1024) {
+    const int j = base + tid;
+    const bool a = j < n && alive[j] != 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, a);
+    const int pre = __popc(bal & ((1u << lane) - 1u));
+    if (lane == 0) warp_tot[w] = __popc(bal);
+    __syncthreads();
+    int off = 0, tot = 0;
+    for (int i = 0; i < 32; ++i) {   // 32 warp totals: trivial serial scan per thread
+      if (i < w) off += warp_tot[i];
+      tot += warp_tot[i];
+    }
+    if (j < n) new_idx[j] = a ? running + off + pre : -1;
+    __syncthreads();
+    if (tid == 0) running += tot;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int n_new = running;
+    state[1] = n_new;
+    state[2] = 1;
+  }
+}
+
+struct CompactBufs {
+  __nv_bfloat16 *cur[B200GRU_MAX_LAYERS];   // hidden state after this step
+  __nv_bfloat16 *tmp[B200GRU_MAX_LAYERS];   // the other ping-pong buffer (free until the next step writes it)
+  int layers, H, pw_log2, bpad;
+};
+
+// one warp per row: move the row's hidden state of every layer to its new place (in tmp)
+__global__ void compact_move_kernel(const int *state, const int32_t *__restrict__ new_idx, CompactBufs b,
+                                    const int32_t *__restrict__ chars, int32_t *__restrict__ chars2,
+                                    const int32_t *__restrict__ slot_row, int32_t *__restrict__ slot2) {
+  if (!state[2]) return;
+  const int n = state[0];
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < n; row += warps) {
+    const int d = new_idx[row];
+    if (d < 0) continue;
+    for (int l = 0; l < b.layers; ++l)
+      for (int c = lane * 8; c < b.H; c += 256)
+        *reinterpret_cast<uint4 *>(b.tmp[l] + h_offset(d, c, b.pw_log2, b.bpad)) =
+            *reinterpret_cast<const uint4 *>(b.cur[l] + h_offset(row, c, b.pw_log2, b.bpad));
+    if (lane == 0) {
+      chars2[d] = chars[row];
+      slot2[d] = slot_row[row];
+    }
+  }
+}
+
+// copy the packed rows back and publish the new row count
+__global__ void compact_commit_kernel(int *state, CompactBufs b, int32_t *__restrict__ chars,
+                                      const int32_t *__restrict__ chars2, int32_t *__restrict__ slot_row,
+                                      const int32_t *__restrict__ slot2, uint8_t *__restrict__ alive) {
+  if (!state[2]) return;
+  const int n_new = state[1];
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < n_new; row += warps) {
+    for (int l = 0; l < b.layers; ++l)
+      for (int c = lane * 8; c < b.H; c += 256) {
+        const size_t off = h_offset(row, c, b.pw_log2, b.bpad);
+        *reinterpret_cast<uint4 *>(b.cur[l] + off) = *reinterpret_cast<const uint4 *>(b.tmp[l] + off);
+      }
+    if (lane == 0) {
+      chars[row] = chars2[row];
+      slot_row[row] = slot2[row];
+      alive[row] = 1;
+    }
+  }
+  // later kernels read state[0]; nothing in THIS kernel does
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    state[0] = n_new;
+    state[3] = 0;   // every name that had ended is gone from the batch now
   }
 }
 
@@ -1306,6 +1434,11 @@ int tc_prepare(b200gru_model *m) {
   }
   if (m->tp_world == 1 || m->tp_fake)
     if (int rc = make_h_maps(m)) return rc;
+  if (int rc = tc_alloc(m, &m->slot_row, (size_t)m->bpad)) return rc;
+  if (int rc = tc_alloc(m, &m->slot2, (size_t)m->bpad)) return rc;
+  if (int rc = tc_alloc(m, &m->chars2, (size_t)m->bpad)) return rc;
+  if (int rc = tc_alloc(m, &m->new_idx, (size_t)m->bpad)) return rc;
+  if (int rc = tc_alloc(m, &m->cp_state, 4)) return rc;
   if (int rc = tc_alloc(m, &m->w_fc, (size_t)C * ld)) return rc;
   B200_CUDA(cudaMemset(m->w_fc, 0, sizeof(__nv_bfloat16) * (size_t)C * ld));
   to_bf16_kernel<<<blocks((size_t)C * H), TPB>>>(m->P(ix.w_fc()), m->w_fc, (size_t)C * H, H, ld);
@@ -1358,6 +1491,10 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
   const int rows = m_tiles * kTileM;
   const int mt_max = m->bpad / kTileM;
   const uint32_t per_round = (uint32_t)(Hs / kUnitBlock);  // counter bumps per (source, m-tile)
+  // finished names are packed away after steps 1, 3, 5, ... (not with tensor
+  // parallelism, whose counters are per tile, nor with the logits tap, whose
+  // rows are per name)
+  const bool compact = m->compact && W == 1 && m->tp_world == 1 && !m->debug_logits;
   if (head) m->trace_begin(s);
   if (head && W > 1) {
     if (!m->tp_bound) return fail(B200GRU_ERR_STATE, "tensor-parallel model: call b200gru_tp_bind first");
@@ -1371,7 +1508,8 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
     for (int l = 0; l < L; ++l) m->tp_rounds[l][0] = m->tp_rounds[l][1] = 0;
   }
   if (head) {
-    tc_init_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(m->chars, m->alive, n, rows, c.sos);
+    tc_init_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(m->chars, m->alive, m->slot_row, m->cp_state,
+                                                                  n, rows, c.sos);
     ++launches;
     m->trace_mark("init", s);
   }
@@ -1382,6 +1520,7 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
       TcLayer &t = m->tc[l];
       LayerArgs a{};
       a.n = n; a.m_tiles = m_tiles; a.n_blocks = Hs / kUnitBlock;
+      a.n_dev = compact ? m->cp_state : nullptr;
       a.kb_x = l == 0 ? 0 : H / TC_BLOCK_K;  // layer 0: table gather in the epilogue, no x-part GEMM
       if (l == 0) { a.t0q = m->t0q; a.chars = m->chars; a.num_char = C; }
       a.kb_h = (step == 0) ? 0 : H / TC_BLOCK_K;  // h == 0 at step 0 (ref:653-654)
@@ -1463,6 +1602,9 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
     a.b_fc = m->b_fc; a.logits = m->debug_logits ? m->logits : nullptr;
     a.rfloats = io->rfloats; a.output = io->output;
     a.chars = m->chars; a.alive = m->alive;
+    a.n_dev = compact ? m->cp_state : nullptr;
+    a.slot_row = compact ? m->slot_row : nullptr;
+    a.gone = compact ? m->cp_state + 3 : nullptr;
     a.tp_world = W; a.tp_rank = R; a.kb_rank = Hs / TC_BLOCK_K; a.flag_stride = mt_max;
     a.pw_log2 = m->pw_log2; a.bpad = m->bpad;
     if (W > 1) {
@@ -1484,6 +1626,19 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
     }
     ++launches;
     m->trace_mark("fc_sample", s);
+    if (compact && (step & 1) && step + 1 < T) {
+      CompactBufs cb{};
+      cb.layers = L; cb.H = H; cb.pw_log2 = m->pw_log2; cb.bpad = m->bpad;
+      for (int l = 0; l < L; ++l) { cb.cur[l] = m->tc[l].h[wr]; cb.tmp[l] = m->tc[l].h[rd]; }
+      const unsigned mv_blocks = (unsigned)(rows < 8 * 1184 ? (rows + 7) / 8 : 1184);  // 8 rows (warps) per block
+      compact_plan_kernel<<<1, 1024, 0, s>>>(m->alive, m->new_idx, m->cp_state);
+      compact_move_kernel<<<mv_blocks, 256, 0, s>>>(m->cp_state, m->new_idx, cb, m->chars, m->chars2, m->slot_row,
+                                                    m->slot2);
+      compact_commit_kernel<<<mv_blocks, 256, 0, s>>>(m->cp_state, cb, m->chars, m->chars2, m->slot_row, m->slot2,
+                                                      m->alive);
+      launches += 3;
+      m->trace_mark("compact", s);
+    }
   }
   if (tail && W > 1) {
     // Zero this rank's counters before announcing the end of the call.  Every

@@ -61,6 +61,11 @@ struct b200gru_model {
   int ldh = 0;                       // row stride (elements) of hidden buffers and K=H weights
                                      // (H + B200GRU_LD_PAD; padding measured: no effect, default 0)
   int pw_log2 = 0;                   // hidden buffers: [H/pw panels][bpad][pw], pw = 1 << pw_log2
+  // compaction of finished names (multi-launch path)
+  bool compact = true;               // B200GRU_COMPACT=0 / b200gru_model_set_compaction turn it off
+  int32_t *slot_row = nullptr, *slot2 = nullptr;   // [bpad] original name of every row (+ scratch)
+  int32_t *chars2 = nullptr, *new_idx = nullptr;   // [bpad] scratch
+  int *cp_state = nullptr;           // [0] rows in use, [1] rows after the planned compaction, [2] carry it out
   __nv_bfloat16 *t0q = nullptr;      // [H/64][C][2][2][n|r|z][16] folded layer-0 input table (epilogue gather)
   bool use_pdl = true;               // programmatic dependent launch between the step kernels
   bool use_pairs = true;             // cta_group::2 layer kernel (B200GRU_CTA_PAIRS=0 disables)

@@ -59,6 +59,7 @@ def _declare(lib):
         "b200gru_last_launch_count": (c_int, [c_void_p]),
         "b200gru_model_set_debug": (c_int, [c_void_p, c_int]),
         "b200gru_model_set_path": (c_int, [c_void_p, c_int, c_int]),
+        "b200gru_model_set_compaction": (c_int, [c_void_p, c_int]),
         "b200gru_debug_build": (c_int, []),
         "b200gru_model_check": (c_int, [c_void_p]),
         "b200gru_model_persist_timeline": (c_int, [c_void_p, c_void_p, c_int]),

@@ -138,6 +138,11 @@ class NameGenerator:
         code = {"auto": 0, "multi": 1, "persistent": 2}[path]
         return bool(_native.check(self._lib.b200gru_model_set_path(self._h, code, persist_max_names), "set_path"))
 
+    def set_compaction(self, on: bool = True) -> None:
+        """Multi-launch path: pack still-running names to the front of the batch
+        a few times per call so finished names stop costing GEMM rows."""
+        _native.check(self._lib.b200gru_model_set_compaction(self._h, 1 if on else 0), "set_compaction")
+
     def check(self) -> None:
         """Debug build (`B200GRU_DEBUG=1`): verify the guard bands around every
         device buffer of the model now; raises on damage.  No-op in release."""

@@ -192,6 +192,16 @@ int b200gru_debug_logits(b200gru_model *m, float *dst_device, int n,
  * Environment: B200GRU_PATH, B200GRU_PERSIST_MAX set the defaults at create. */
 int b200gru_model_set_path(b200gru_model *m, int path, int persist_max_names);
 
+/* Multi-launch tensor-core path: pack the names that are still running to the
+ * front of the batch after steps 1, 3, 5, ... so that finished names stop
+ * occupying GEMM rows (the reference stops a name at EOS, ref:881-882).  Each
+ * point is three small launches that do nothing unless a whole 256-name tile
+ * can be dropped; rows of the output keep their positions (a row map goes with
+ * the names).  On by default (B200GRU_COMPACT=0 at create turns it off); off
+ * while the logits tap is on and for tensor-parallel models.  The persistent
+ * path skips finished 256-name tiles instead. */
+int b200gru_model_set_compaction(b200gru_model *m, int on);
+
 /* Debug build (libb200gru_debug.so, compiled with -DB200GRU_DEBUG; selected by
  * B200GRU_DEBUG=1 in the Python package).  It stands in for compute-sanitizer,
  * which this GPU pool does not allow: device-side assertions on computed global

@@ -126,10 +126,12 @@ def test_trace_reports_every_launch(gen_tiny, tiny_cfg):
     n = 300
     r = W.random_floats(n * tiny_cfg.max_len, 25)
     gen_tiny.set_path("multi")      # the per-layer launches; the persistent path is one span
+    gen_tiny.set_compaction(False)  # (its three launches per point share one span)
     gen_tiny.set_trace(True)
     gen_tiny.generate(n, r, mode="tc")
     tr = gen_tiny.trace()
     gen_tiny.set_trace(False)
+    gen_tiny.set_compaction(True)
     gen_tiny.set_path("auto")
     assert len(tr) == gen_tiny.last_launches == 1 + tiny_cfg.max_len * (tiny_cfg.num_layers + 1)
     assert [k for k, _ in tr[:4]] == ["init", "layer0", "layerN", "fc_sample"]
@@ -154,3 +156,33 @@ def test_tc_character_distribution_matches_exact(gen_tiny, tiny_cfg):
     # so chi2 is far below dof; dof + 4*sqrt(2*dof) would already be generous
     assert chi2 < dof + 4 * (2 * dof) ** 0.5, (chi2, dof)
     assert (tc == ex).double().mean() > 0.9
+
+
+@pytest.mark.parametrize("shape", ["tiny", "default"])
+def test_compaction_of_finished_names_changes_nothing_but_the_time(shape, tiny_cfg):
+    """EOS made likely: most names end early, the multi-launch path packs the
+    survivors to the front after steps 1, 3, 5, ... and later kernels run fewer
+    tiles.  Rows must be bit-identical to a run with compaction off (a row's
+    arithmetic does not depend on where in the batch it sits)."""
+    cfg = tiny_cfg if shape == "tiny" else GRUConfig()
+    p = W.random_init(cfg, 3)
+    W.split(cfg, p)["b_fc"][cfg.eos] = 3.0 if shape == "tiny" else 4.4     # P(EOS) ~ 0.25 per step
+    n = 3000 if shape == "tiny" else 4096
+    r = W.random_floats(n * cfg.max_len, 71)
+    with NameGenerator(cfg, p, device=0, max_batch=n) as g:
+        g.set_path("multi")
+        on = g.generate(n, r)
+        launches_on = g.last_launches
+        again = g.generate(n, r)           # graph replay, state fully reset per call
+        g.set_compaction(False)
+        off = g.generate(n, r)
+        launches_off = g.last_launches
+        ex = g.generate(n, r, mode="exact") if shape == "tiny" else None
+    assert torch.equal(on, off)
+    assert torch.equal(on, again)
+    assert launches_on > launches_off
+    T = cfg.max_len
+    ended = (on[:, :T] == cfg.eos).any(dim=1).float().mean().item()
+    assert ended > 0.5, ended
+    if ex is not None:
+        assert (on == ex).all(dim=1).float().mean() > 0.9
