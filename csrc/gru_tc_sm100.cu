@@ -1630,7 +1630,9 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
       CompactBufs cb{};
       cb.layers = L; cb.H = H; cb.pw_log2 = m->pw_log2; cb.bpad = m->bpad;
       for (int l = 0; l < L; ++l) { cb.cur[l] = m->tc[l].h[wr]; cb.tmp[l] = m->tc[l].h[rd]; }
-      const unsigned mv_blocks = (unsigned)(rows < 8 * 1184 ? (rows + 7) / 8 : 1184);  // 8 rows (warps) per block
+      // 8 warps (rows) per block, grid-stride; two blocks per SM keep the early
+      // exit of an unneeded compaction at ~2 us per launch
+      const unsigned mv_blocks = (unsigned)(rows < 8 * 296 ? (rows + 7) / 8 : 296);
       compact_plan_kernel<<<1, 1024, 0, s>>>(m->alive, m->new_idx, m->cp_state);
       compact_move_kernel<<<mv_blocks, 256, 0, s>>>(m->cp_state, m->new_idx, cb, m->chars, m->chars2, m->slot_row,
                                                     m->slot2);
