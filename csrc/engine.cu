@@ -228,6 +228,7 @@ int b200gru_model_create_tp(const b200gru_config *cfg, const float *params,
     if (const char *e = getenv("B200GRU_PATH")) m->ps_path = atoi(e);
     if (const char *e = getenv("B200GRU_PERSIST_MAX")) m->ps_max_n = atoi(e);
     if (const char *e = getenv("B200GRU_COMPACT")) m->compact = e[0] != '0';
+    if (const char *e = getenv("B200GRU_COMPACT_MIN")) m->compact_min_n = atoi(e);
   }
   {
     const char *e = getenv("B200GRU_TP_FAKE");

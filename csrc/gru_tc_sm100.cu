@@ -1494,7 +1494,8 @@ int tc_generate(b200gru_model *m, int n, const b200gru_io *io, cudaStream_t s, i
   // finished names are packed away after steps 1, 3, 5, ... (not with tensor
   // parallelism, whose counters are per tile, nor with the logits tap, whose
   // rows are per name)
-  const bool compact = m->compact && W == 1 && m->tp_world == 1 && !m->debug_logits;
+  // ... nor for small calls, where the twelve extra launches cost more than dropped tiles can save
+  const bool compact = m->compact && W == 1 && m->tp_world == 1 && !m->debug_logits && n >= m->compact_min_n;
   if (head) m->trace_begin(s);
   if (head && W > 1) {
     if (!m->tp_bound) return fail(B200GRU_ERR_STATE, "tensor-parallel model: call b200gru_tp_bind first");

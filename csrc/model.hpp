@@ -63,6 +63,7 @@ struct b200gru_model {
   int pw_log2 = 0;                   // hidden buffers: [H/pw panels][bpad][pw], pw = 1 << pw_log2
   // compaction of finished names (multi-launch path)
   bool compact = true;               // B200GRU_COMPACT=0 / b200gru_model_set_compaction turn it off
+  int compact_min_n = 8192;          // calls with fewer names never compact (B200GRU_COMPACT_MIN)
   int32_t *slot_row = nullptr, *slot2 = nullptr;   // [bpad] original name of every row (+ scratch)
   int32_t *chars2 = nullptr, *new_idx = nullptr;   // [bpad] scratch
   int *cp_state = nullptr;           // [0] rows in use, [1] rows after the planned compaction, [2] carry it out

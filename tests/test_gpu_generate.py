@@ -1,4 +1,6 @@
 """GPU kernels vs the CPU oracles (SURVEY §4 'Kernel' tier)."""
+import os
+
 import pytest
 import torch
 
@@ -169,7 +171,12 @@ def test_compaction_of_finished_names_changes_nothing_but_the_time(shape, tiny_c
     W.split(cfg, p)["b_fc"][cfg.eos] = 3.0 if shape == "tiny" else 4.4     # P(EOS) ~ 0.25 per step
     n = 3000 if shape == "tiny" else 4096
     r = W.random_floats(n * cfg.max_len, 71)
-    with NameGenerator(cfg, p, device=0, max_batch=n) as g:
+    os.environ["B200GRU_COMPACT_MIN"] = "0"      # small calls skip compaction by default
+    try:
+        g = NameGenerator(cfg, p, device=0, max_batch=n)
+    finally:
+        del os.environ["B200GRU_COMPACT_MIN"]
+    with g:
         g.set_path("multi")
         on = g.generate(n, r)
         launches_on = g.last_launches
