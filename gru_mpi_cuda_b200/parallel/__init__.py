@@ -11,4 +11,7 @@ def __getattr__(name):  # lazy: dp/symm import torch.distributed
     if name == "SymmBuffer":
         from .symm import SymmBuffer
         return SymmBuffer
+    if name == "McBuffer":
+        from .symm import McBuffer
+        return McBuffer
     raise AttributeError(name)
