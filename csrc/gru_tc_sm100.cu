@@ -63,7 +63,8 @@ constexpr int L_STAGE_BYTES = TC_A_BYTES + L_B_BYTES;
 constexpr int L_STAGES = 4;
 constexpr int OUT_TILE_BYTES = kTileM * 128;  // 128 names x 64 units bf16, 128B-swizzled
 // [align slack 1024][stages][barrier block 1024][2 staging tiles]
-constexpr int L_SMEM_BYTES = 1024 + L_STAGES * L_STAGE_BYTES + 1024 + 2 * OUT_TILE_BYTES;
+constexpr int OUT_TILES = 3;                  // staging tiles: the store of tile i-1 may still be reading while i+1 is written
+constexpr int L_SMEM_BYTES = 1024 + L_STAGES * L_STAGE_BYTES + 1024 + OUT_TILES * OUT_TILE_BYTES;
 constexpr int EPI_BAR_ID = 1;                 // named barrier of the epilogue warps
 
 
@@ -264,13 +265,17 @@ struct PubRing {
 __device__ __forceinline__ void epilogue_store_tile(const CUtensorMap *map_out, const LayerArgs &args,
                                                     uint8_t *stage_tile, int col, int m_tile,
                                                     bool issuer, int tid, const PubRing &pub, int it) {
-  fence_proxy_async_smem();                       // generic smem writes -> async proxy
+  // (every thread has already fenced its staging writes towards the async proxy)
   named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);   // the staged tile is complete
   if (issuer) {
     int ci, co;
     h_coords(m_tile * kTileM, col, args.pw_log2, args.bpad, &ci, &co);
     tma_store_2d(map_out, stage_tile, ci, co);
     tma_store_commit();
+    // With three staging tiles this is the only reuse guard needed: the store of
+    // the PREVIOUS tile has finished reading before this thread reaches the next
+    // tile's barrier, i.e. before anyone writes the tile after that (same buffer).
+    tma_store_wait_read<1>();
   }
   if (args.tp_world > 1) {
 #pragma unroll
@@ -573,10 +578,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       const int col = args.col0 + n_blk * 64;
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
-      uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
-      // the TMA store that read this staging buffer two tiles ago is done
-      if (issuer) tma_store_wait_read<1>();
-      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
+      uint8_t *stage_tile = stage_out + (it % OUT_TILES) * OUT_TILE_BYTES;
 
       const bool has_acc = kb_total > 0;
       if (has_acc) {
@@ -585,6 +587,9 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
       }
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
       gate_epilogue<LAYER0>(t, hq, bias4, stage_tile, r, half, tq, has_acc);
+      // staging writes -> async proxy, NOW: issued after the next tile's global
+      // loads below, this fence would wait for them (an L2 round trip per tile)
+      fence_proxy_async_smem();
       if (has_acc) {
         tc_fence_before();
         __syncwarp();
@@ -622,7 +627,7 @@ gru_layer_kernel(const __grid_constant__ CUtensorMap map_x,
 constexpr int P_B_BYTES = 96 * 128;          // 12 KB: this CTA's half of B
 constexpr int P_STAGE_BYTES = TC_A_BYTES + P_B_BYTES;
 constexpr int P_STAGES = 6;
-constexpr int P_SMEM_BYTES = 1024 + P_STAGES * P_STAGE_BYTES + 1024 + 2 * OUT_TILE_BYTES;
+constexpr int P_SMEM_BYTES = 1024 + P_STAGES * P_STAGE_BYTES + 1024 + OUT_TILES * OUT_TILE_BYTES;
 
 template <bool LAYER0>
 __global__ void __launch_bounds__(L_THREADS, 1)
@@ -810,9 +815,7 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       const int col = args.col0 + n_blk * 64;
       const float4 *bias4 =
           reinterpret_cast<const float4 *>(args.bias + (size_t)n_blk * 4 * 64 + half * 32);
-      uint8_t *stage_tile = stage_out + (it & 1) * OUT_TILE_BYTES;
-      if (issuer) tma_store_wait_read<1>();
-      named_bar_sync(EPI_BAR_ID, L_EPI_WARPS * 32);
+      uint8_t *stage_tile = stage_out + (it % OUT_TILES) * OUT_TILE_BYTES;
 
       const bool has_acc = kb_total > 0;
       if (has_acc) {
@@ -821,6 +824,9 @@ gru_layer_pair_kernel(const __grid_constant__ CUtensorMap map_x,
       }
       const uint32_t t = tmem_base + lane_base + acc_stage * TC_ACC_STRIDE + half * 32;
       gate_epilogue<LAYER0>(t, hq, bias4, stage_tile, r, half, tq, has_acc);
+      // staging writes -> async proxy, NOW: issued after the next tile's global
+      // loads below, this fence would wait for them (an L2 round trip per tile)
+      fence_proxy_async_smem();
       if (has_acc) {
         tc_fence_before();
         __syncwarp();
